@@ -1,0 +1,155 @@
+"""ctypes binding of libb200dp.so (the C ABI declared in include/b200dp.h).
+
+There is deliberately no fallback: if the shared library is missing or a call
+returns an error, the caller gets an exception.  Build the library with
+``python -c "import __graft_entry__ as g; g.build()"`` (nvcc, sm_100a).
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+import threading
+from ctypes import POINTER, Structure, c_char_p, c_float, c_int, c_int32, c_int64, c_size_t, c_uint32, c_void_p
+
+PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+CSRC_DIR = os.path.join(PKG_DIR, "csrc")
+LIB_PATH = os.path.join(PKG_DIR, "libb200dp.so")
+SOURCES = ["augment.cu", "bn.cu", "comm.cu", "update.cu"]
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+    "-Xcompiler", "-fPIC", "-shared",
+]
+
+F32, BF16 = 0, 1
+OPT_NONE, OPT_SGD, OPT_ADAM = 0, 1, 2
+MAX_WORLD = 8
+COMM_HANDLE_BYTES = 128
+
+
+class B200DPError(RuntimeError):
+    """A libb200dp entry point returned a non-zero code."""
+
+
+class OptArgs(Structure):
+    """Mirror of ``b200dp_opt_args`` (include/b200dp.h)."""
+
+    _fields_ = [
+        ("kind", c_int), ("lr", c_float), ("momentum", c_float), ("dampening", c_float),
+        ("nesterov", c_int), ("first_step", c_int), ("weight_decay", c_float),
+        ("beta1", c_float), ("beta2", c_float), ("eps", c_float),
+        ("step_size", c_float), ("bias_correction2_sqrt", c_float),
+    ]
+
+
+def _sources():
+    hdrs = [os.path.join(CSRC_DIR, "common.cuh"), os.path.join(PKG_DIR, "..", "include", "b200dp.h")]
+    return [os.path.join(CSRC_DIR, s) for s in SOURCES], hdrs
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    """Compile csrc/*.cu into libb200dp.so with nvcc for sm_100a (no GPU needed)."""
+    srcs, hdrs = _sources()
+    if not force and os.path.exists(LIB_PATH):
+        newest = max(os.path.getmtime(p) for p in srcs + hdrs if os.path.exists(p))
+        if os.path.getmtime(LIB_PATH) >= newest:
+            return LIB_PATH
+    nvcc = os.environ.get("NVCC", "nvcc")
+    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_PATH] + srcs
+    proc = subprocess.run(cmd, capture_output=True, text=True, stdin=subprocess.DEVNULL, timeout=1200)
+    if proc.returncode != 0:
+        raise B200DPError("nvcc failed:\n" + proc.stdout + proc.stderr)
+    if verbose:
+        print(proc.stderr)
+    return LIB_PATH
+
+
+_lock = threading.Lock()
+_lib = None
+
+_VP = c_void_p
+_SIGNATURES = {
+    # name: (restype, argtypes)
+    "b200dp_version": (c_int, []),
+    "b200dp_error_string": (c_char_p, [c_int]),
+    "b200dp_augment_u8_bf16": (c_int, [_VP, c_int, c_int, c_int, _VP, c_int, c_int, c_int,
+                                       POINTER(c_float), POINTER(c_float), _VP, _VP]),
+    "b200dp_bn_scratch_bytes": (c_size_t, [c_int]),
+    "b200dp_bn_fwd_stats": (c_int, [_VP, c_int, c_int64, c_int, _VP, _VP, _VP, c_uint32, _VP]),
+    "b200dp_bn_fwd_apply": (c_int, [_VP, _VP, _VP, c_int, c_int64, c_int, _VP, _VP, _VP, c_float,
+                                    c_float, _VP, _VP, _VP, _VP, _VP, c_int, _VP, c_uint32, _VP]),
+    "b200dp_bn_inference": (c_int, [_VP, _VP, _VP, c_int, c_int64, c_int, _VP, _VP, _VP, _VP,
+                                    c_float, c_int, _VP]),
+    "b200dp_bn_bwd_reduce": (c_int, [_VP, _VP, _VP, c_int, c_int64, c_int, _VP, _VP, _VP, _VP,
+                                     c_int, _VP, _VP, _VP, _VP, _VP, c_uint32, _VP]),
+    "b200dp_bn_bwd_apply": (c_int, [_VP, _VP, _VP, _VP, _VP, c_int, c_int64, c_int, _VP, _VP, _VP,
+                                    _VP, _VP, _VP, c_int, _VP, c_uint32, _VP]),
+    "b200dp_comm_create": (c_int, [c_int, c_int, c_size_t, POINTER(_VP)]),
+    "b200dp_comm_export": (c_int, [_VP, _VP]),
+    "b200dp_comm_open_peers": (c_int, [_VP, _VP]),
+    "b200dp_comm_destroy": (c_int, [_VP]),
+    "b200dp_comm_rank": (c_int, [_VP]),
+    "b200dp_comm_world": (c_int, [_VP]),
+    "b200dp_comm_heap": (_VP, [_VP, c_int]),
+    "b200dp_comm_heap_bytes": (c_size_t, [_VP]),
+    "b200dp_comm_next_seq": (c_uint32, [_VP]),
+    "b200dp_comm_barrier": (c_int, [_VP, _VP]),
+    "b200dp_comm_error": (c_int, [_VP]),
+    "b200dp_bucket_pack": (c_int, [POINTER(_VP), POINTER(c_int64), POINTER(c_int64), c_int, _VP,
+                                   c_int, c_float, _VP]),
+    "b200dp_allreduce_update": (c_int, [_VP, c_size_t, c_int, c_size_t, c_int, c_int64, c_int64,
+                                        _VP, _VP, _VP, POINTER(OptArgs), c_int, c_int, c_int,
+                                        c_uint32, _VP]),
+}
+
+
+def exported_symbols():
+    """Names every build of the library must export (checked by the CPU tests)."""
+    return sorted(_SIGNATURES)
+
+
+def lib() -> ctypes.CDLL:
+    """Load libb200dp.so once; raise if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is None:
+            if not os.path.exists(LIB_PATH):
+                raise B200DPError(
+                    f"{LIB_PATH} is missing: build it with __graft_entry__.build() (nvcc, sm_100a). "
+                    "This package has no CPU or eager fallback.")
+            handle = ctypes.CDLL(LIB_PATH)
+            for name, (res, args) in _SIGNATURES.items():
+                fn = getattr(handle, name)  # AttributeError if the symbol is not exported
+                fn.restype = res
+                fn.argtypes = args
+            _lib = handle
+    return _lib
+
+
+def check(rc: int, what: str = "") -> None:
+    if rc != 0:
+        msg = lib().b200dp_error_string(rc).decode()
+        raise B200DPError(f"{what or 'libb200dp'} failed with code {rc}: {msg}")
+
+
+def dtype_code(dtype) -> int:
+    import torch
+
+    if dtype == torch.float32:
+        return F32
+    if dtype == torch.bfloat16:
+        return BF16
+    raise B200DPError(f"libb200dp handles float32 and bfloat16 tensors, not {dtype}")
+
+
+def ptr(t) -> int:
+    """Device (or pinned host) address of a tensor, 0 for None."""
+    return 0 if t is None else t.data_ptr()
+
+
+def current_stream() -> int:
+    import torch
+
+    return torch.cuda.current_stream().cuda_stream

@@ -1,0 +1,118 @@
+"""Host side of the communicator: rendezvous of CUDA IPC handles over an existing
+``torch.distributed`` process group, and tensor views of the symmetric heap.
+
+Stands where ``dist.init_process_group("nccl")`` + ProcessGroupNCCL stand for the
+gradient path of the reference (01_torch_distributor/01_basic_torch_distributor.py:269,291):
+the process group (gloo or NCCL, whatever the launcher set up) is only used once,
+to all-gather 128-byte handle blobs; after that the ranks talk through peer
+loads/stores issued by the kernels in csrc/.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+
+from . import _lib
+
+
+class _RawCudaBuffer:
+    """Exposes a raw device allocation through ``__cuda_array_interface__``."""
+
+    def __init__(self, ptr: int, nbytes: int, owner):
+        self.owner = owner  # keeps the communicator (and so the allocation) alive
+        self.__cuda_array_interface__ = {
+            "shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2, "strides": None,
+        }
+
+
+class Communicator:
+    """One per process and use: owns ``heap_bytes`` of peer-visible device memory.
+
+    ``process_group`` (default: the global group) must already be initialised
+    when world size > 1; with no initialised group the communicator is a
+    single-rank one and nothing is exchanged.
+    """
+
+    def __init__(self, process_group=None, heap_bytes: int = 0, device: Optional[torch.device] = None):
+        if dist.is_available() and dist.is_initialized():
+            self.rank = dist.get_rank(process_group)
+            self.world = dist.get_world_size(process_group)
+        else:
+            self.rank, self.world = 0, 1
+        if self.world not in (1, 2, 4, 8):
+            raise _lib.B200DPError(f"world size {self.world} is not supported (1, 2, 4 or 8 GPUs of one node)")
+        self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        self.process_group = process_group
+        lib = _lib.lib()
+        self._handle = ctypes.c_void_p()
+        with torch.cuda.device(self.device):
+            _lib.check(lib.b200dp_comm_create(self.rank, self.world, int(heap_bytes), ctypes.byref(self._handle)),
+                       "b200dp_comm_create")
+            if self.world > 1:
+                blob = ctypes.create_string_buffer(_lib.COMM_HANDLE_BYTES)
+                _lib.check(lib.b200dp_comm_export(self._handle, blob), "b200dp_comm_export")
+                gathered = [None] * self.world
+                dist.all_gather_object(gathered, bytes(blob.raw), group=process_group)
+                allb = ctypes.create_string_buffer(b"".join(gathered), _lib.COMM_HANDLE_BYTES * self.world)
+                _lib.check(lib.b200dp_comm_open_peers(self._handle, allb), "b200dp_comm_open_peers")
+                # nobody may touch a peer's flags before every rank has mapped them
+                dist.barrier(group=process_group)
+        self.heap_bytes = int(lib.b200dp_comm_heap_bytes(self._handle))
+        self._heap_ptr = int(lib.b200dp_comm_heap(self._handle, self.rank))
+        self._heap_u8 = torch.as_tensor(_RawCudaBuffer(self._heap_ptr, self.heap_bytes, self), device=self.device)
+
+    # -- C handle ------------------------------------------------------------------
+    @property
+    def handle(self) -> ctypes.c_void_p:
+        if not self._handle:
+            raise _lib.B200DPError("communicator was destroyed")
+        return self._handle
+
+    def next_seq(self) -> int:
+        return int(_lib.lib().b200dp_comm_next_seq(self.handle))
+
+    def barrier(self) -> None:
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().b200dp_comm_barrier(self.handle, _lib.current_stream()), "b200dp_comm_barrier")
+
+    def check_error(self) -> None:
+        """Raise if a kernel on this rank timed out waiting for a peer."""
+        rc = _lib.lib().b200dp_comm_error(self.handle)
+        if rc != 0:
+            raise _lib.B200DPError("a libb200dp kernel gave up waiting for a peer rank (peer dead or out of step)")
+
+    # -- heap views ----------------------------------------------------------------
+    def heap_view(self, byte_offset: int, numel: int, dtype: torch.dtype) -> torch.Tensor:
+        """A tensor over ``numel`` elements of the LOCAL heap starting at ``byte_offset``."""
+        nbytes = numel * torch.empty((), dtype=dtype).element_size()
+        if byte_offset % 16 or byte_offset + nbytes > self.heap_bytes:
+            raise _lib.B200DPError("heap view out of range or misaligned")
+        return self._heap_u8[byte_offset:byte_offset + nbytes].view(dtype)
+
+    def destroy(self) -> None:
+        if self._handle:
+            self._heap_u8 = None
+            _lib.lib().b200dp_comm_destroy(self._handle)
+            self._handle = ctypes.c_void_p()
+
+
+_stats_comms = {}
+
+
+def stats_communicator(process_group=None) -> Communicator:
+    """Process-wide communicator used by SyncBatchNorm layers (no heap needed)."""
+    key = (id(process_group) if process_group is not None else None, torch.cuda.current_device())
+    comm = _stats_comms.get(key)
+    if comm is None:
+        comm = Communicator(process_group, heap_bytes=0)
+        _stats_comms[key] = comm
+    return comm
+
+
+def reset_stats_communicators() -> None:
+    for comm in _stats_comms.values():
+        comm.destroy()
+    _stats_comms.clear()

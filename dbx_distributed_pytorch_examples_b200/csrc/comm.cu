@@ -1,0 +1,156 @@
+// comm.cu — the communicator: library-owned buffers that every rank maps into
+// its address space with CUDA IPC, so that kernels reach peer HBM with plain
+// loads/stores over NVLink 5 / NVSwitch.  One process per GPU.
+//
+// Each rank owns two cudaMalloc'd blocks:
+//   heap  (heap_bytes)        gradient buckets and module parameters
+//   sync  (b200dp_sync_area)  flags + SyncBN exchange slots, zero-filled once
+// Flags only ever grow (they hold exchange sequence numbers), so nothing is
+// reset between steps and a late reader can never see a "cleared" flag.
+#include <new>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace {
+
+using namespace b200dp;
+
+__global__ void barrier_kernel(b200dp_peers P, uint32_t seq) {
+  const int t = threadIdx.x;
+  if (t < P.world) {
+    __threadfence_system();
+    st_release_sys(&P.sync[t]->barrier[P.rank], seq);
+    if (!wait_flag(&P.sync[P.rank]->barrier[t], seq)) atomicExch(&P.sync[P.rank]->error, 1u);
+  }
+}
+
+struct ExportBlob {
+  cudaIpcMemHandle_t heap;
+  cudaIpcMemHandle_t sync;
+};
+static_assert(sizeof(cudaIpcMemHandle_t) == B200DP_IPC_HANDLE_BYTES, "IPC handle size");
+static_assert(sizeof(ExportBlob) == B200DP_COMM_HANDLE_BYTES, "export blob size");
+
+}  // namespace
+
+extern "C" int b200dp_version(void) { return B200DP_VERSION; }
+
+extern "C" const char* b200dp_error_string(int code) {
+  switch (code) {
+    case B200DP_OK: return "ok";
+    case B200DP_EINVAL: return "b200dp: invalid argument";
+    case B200DP_EUNSUPPORTED: return "b200dp: unsupported shape or dtype";
+    case B200DP_EALIGN: return "b200dp: pointer is not 16-byte aligned";
+    case B200DP_ESTATE: return "b200dp: communicator is not ready (peers not opened?)";
+    case B200DP_ETOOBIG: return "b200dp: size exceeds a fixed limit of this entry point";
+    default: break;
+  }
+  if (code > 0) return cudaGetErrorString((cudaError_t)code);
+  return "b200dp: unknown error";
+}
+
+extern "C" int b200dp_comm_create(int rank, int world, size_t heap_bytes, b200dp_comm** out) {
+  if (!out || world < 1 || world > B200DP_MAX_WORLD || rank < 0 || rank >= world)
+    return B200DP_EINVAL;
+  b200dp_comm* c = new (std::nothrow) b200dp_comm();
+  if (!c) return (int)cudaErrorMemoryAllocation;
+  memset(c, 0, sizeof(*c));
+  c->rank = rank;
+  c->world = world;
+  // a 2 MiB granule keeps every bucket offset aligned however it is carved up
+  c->heap_bytes = ((heap_bytes + (2u << 20) - 1) >> 21) << 21;
+  if (c->heap_bytes == 0) c->heap_bytes = 2u << 20;
+  cudaError_t e = cudaGetDevice(&c->device);
+  void* heap = nullptr;
+  void* sync = nullptr;
+  if (e == cudaSuccess) e = cudaMalloc(&heap, c->heap_bytes);
+  if (e == cudaSuccess) e = cudaMalloc(&sync, sizeof(b200dp_sync_area));
+  if (e == cudaSuccess) e = cudaMemset(sync, 0, sizeof(b200dp_sync_area));
+  if (e == cudaSuccess) e = cudaMemset(heap, 0, c->heap_bytes);
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) {
+    if (heap) cudaFree(heap);
+    if (sync) cudaFree(sync);
+    delete c;
+    return (int)e;
+  }
+  c->heap[rank] = heap;
+  c->sync[rank] = static_cast<b200dp_sync_area*>(sync);
+  c->peers_open = (world == 1);
+  c->seq = 0;
+  *out = c;
+  return B200DP_OK;
+}
+
+extern "C" int b200dp_comm_export(b200dp_comm* comm, void* out) {
+  if (!comm || !out) return B200DP_EINVAL;
+  ExportBlob blob;
+  memset(&blob, 0, sizeof(blob));
+  if (comm->world > 1) {
+    B200DP_CUDA_TRY(cudaIpcGetMemHandle(&blob.heap, comm->heap[comm->rank]));
+    B200DP_CUDA_TRY(cudaIpcGetMemHandle(&blob.sync, comm->sync[comm->rank]));
+  }
+  memcpy(out, &blob, sizeof(blob));
+  return B200DP_OK;
+}
+
+extern "C" int b200dp_comm_open_peers(b200dp_comm* comm, const void* all_handles) {
+  if (!comm || !all_handles) return B200DP_EINVAL;
+  if (comm->peers_open) return B200DP_OK;
+  const ExportBlob* blobs = static_cast<const ExportBlob*>(all_handles);
+  for (int p = 0; p < comm->world; ++p) {
+    if (p == comm->rank) continue;
+    void* heap = nullptr;
+    void* sync = nullptr;
+    B200DP_CUDA_TRY(cudaIpcOpenMemHandle(&heap, blobs[p].heap, cudaIpcMemLazyEnablePeerAccess));
+    B200DP_CUDA_TRY(cudaIpcOpenMemHandle(&sync, blobs[p].sync, cudaIpcMemLazyEnablePeerAccess));
+    comm->heap[p] = heap;
+    comm->sync[p] = static_cast<b200dp_sync_area*>(sync);
+  }
+  comm->peers_open = true;
+  return B200DP_OK;
+}
+
+extern "C" int b200dp_comm_destroy(b200dp_comm* comm) {
+  if (!comm) return B200DP_OK;
+  cudaDeviceSynchronize();
+  for (int p = 0; p < comm->world; ++p) {
+    if (p == comm->rank) continue;
+    if (comm->heap[p]) cudaIpcCloseMemHandle(comm->heap[p]);
+    if (comm->sync[p]) cudaIpcCloseMemHandle(comm->sync[p]);
+  }
+  if (comm->heap[comm->rank]) cudaFree(comm->heap[comm->rank]);
+  if (comm->sync[comm->rank]) cudaFree(comm->sync[comm->rank]);
+  delete comm;
+  return B200DP_OK;
+}
+
+extern "C" int b200dp_comm_rank(const b200dp_comm* comm) { return comm ? comm->rank : -1; }
+extern "C" int b200dp_comm_world(const b200dp_comm* comm) { return comm ? comm->world : -1; }
+extern "C" void* b200dp_comm_heap(b200dp_comm* comm, int peer) {
+  if (!comm || peer < 0 || peer >= comm->world) return nullptr;
+  return comm->heap[peer];
+}
+extern "C" size_t b200dp_comm_heap_bytes(const b200dp_comm* comm) {
+  return comm ? comm->heap_bytes : 0;
+}
+extern "C" uint32_t b200dp_comm_next_seq(b200dp_comm* comm) { return comm ? ++comm->seq : 0; }
+
+extern "C" int b200dp_comm_barrier(b200dp_comm* comm, b200dp_stream_t stream) {
+  if (!comm) return B200DP_EINVAL;
+  if (!comm->peers_open) return B200DP_ESTATE;
+  if (comm->world == 1) return B200DP_OK;
+  const uint32_t seq = ++comm->seq;
+  barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(b200dp_make_peers(comm), seq);
+  B200DP_LAUNCH_CHECK();
+  return B200DP_OK;
+}
+
+// Non-zero once any kernel on this rank gave up waiting for a peer.
+extern "C" int b200dp_comm_error(b200dp_comm* comm) {
+  if (!comm) return B200DP_EINVAL;
+  uint32_t v = 0;
+  B200DP_CUDA_TRY(cudaMemcpy(&v, &comm->sync[comm->rank]->error, sizeof(v), cudaMemcpyDeviceToHost));
+  return (int)v;
+}

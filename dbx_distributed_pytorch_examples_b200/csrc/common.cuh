@@ -1,0 +1,192 @@
+// common.cuh — shared device helpers for libb200dp (sm_100a only).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/b200dp.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "libb200dp is written for sm_100a (Blackwell B200) only"
+#endif
+
+#define B200DP_NUM_SMS 148
+
+#define B200DP_CUDA_TRY(expr)                 \
+  do {                                        \
+    cudaError_t _e = (expr);                  \
+    if (_e != cudaSuccess) return (int)_e;    \
+  } while (0)
+
+// A launch error must not stay sticky in the runtime's last-error slot.
+#define B200DP_LAUNCH_CHECK()                 \
+  do {                                        \
+    cudaError_t _e = cudaGetLastError();      \
+    if (_e != cudaSuccess) return (int)_e;    \
+  } while (0)
+
+namespace b200dp {
+
+// ---- 128-bit streaming loads / stores --------------------------------------
+// Activations are read once per pass: keep them out of L1 and mark them
+// evict-first so they do not push the small per-channel tables out of L2.
+__device__ __forceinline__ uint64_t evict_first_policy() {
+  uint64_t pol;
+  asm("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ uint4 ld_stream(const void* p) {
+  uint4 r;
+  const uint64_t pol = evict_first_policy();  // not volatile: hoisted out of loops
+  asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p), "l"(pol));
+  return r;
+}
+// Same, but leaves the line in L2 with normal priority: for a first pass whose
+// data the next kernel reads again (statistics before normalise, reduce before
+// apply); layers smaller than the 126 MB L2 then take their second pass from L2.
+__device__ __forceinline__ uint4 ld_keep(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+// Plain coherent 128-bit load (data another kernel or peer may have written).
+__device__ __forceinline__ uint4 ld_cg(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void st_stream(void* p, const uint4& v) {
+  asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x),
+               "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ float ld_cg_f32(const float* p) {
+  float r;
+  asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(r) : "l"(p));
+  return r;
+}
+
+// ---- system-scope flags (cross-GPU signalling over NVLink) ------------------
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+// Spin until *p has reached `seq` (wrap-safe).  Returns false on timeout so a
+// dead peer turns into an error flag instead of a hung GPU.
+__device__ __forceinline__ bool wait_flag(const uint32_t* p, uint32_t seq) {
+  long long t0 = clock64();
+  while ((int32_t)(ld_acquire_sys(p) - seq) < 0) {
+    __nanosleep(20);
+    if (clock64() - t0 > (20LL << 30)) return false;  // ~10 s at 2 GHz
+  }
+  return true;
+}
+
+// ---- bf16 <-> fp32 on packed words -----------------------------------------
+__device__ __forceinline__ float bf16lo(uint32_t w) { return __uint_as_float(w << 16); }
+__device__ __forceinline__ float bf16hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+// A 16-byte vector of T seen as floats: 4 (fp32) or 8 (bf16) lanes.
+template <typename T>
+struct Vec;
+template <>
+struct Vec<float> {
+  static constexpr int N = 4;
+  __device__ __forceinline__ static void unpack(const uint4& r, float* f) {
+    f[0] = __uint_as_float(r.x);
+    f[1] = __uint_as_float(r.y);
+    f[2] = __uint_as_float(r.z);
+    f[3] = __uint_as_float(r.w);
+  }
+  __device__ __forceinline__ static uint4 pack(const float* f) {
+    return make_uint4(__float_as_uint(f[0]), __float_as_uint(f[1]), __float_as_uint(f[2]),
+                      __float_as_uint(f[3]));
+  }
+};
+template <>
+struct Vec<__nv_bfloat16> {
+  static constexpr int N = 8;
+  __device__ __forceinline__ static void unpack(const uint4& r, float* f) {
+    f[0] = bf16lo(r.x);
+    f[1] = bf16hi(r.x);
+    f[2] = bf16lo(r.y);
+    f[3] = bf16hi(r.y);
+    f[4] = bf16lo(r.z);
+    f[5] = bf16hi(r.z);
+    f[6] = bf16lo(r.w);
+    f[7] = bf16hi(r.w);
+  }
+  __device__ __forceinline__ static uint4 pack(const float* f) {
+    return make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]),
+                      pack_bf16(f[6], f[7]));
+  }
+};
+
+__host__ __device__ __forceinline__ bool aligned16(const void* p) {
+  return (reinterpret_cast<uintptr_t>(p) & 15u) == 0;
+}
+
+}  // namespace b200dp
+
+// ---- communicator layout (comm.cu owns it; bn.cu / update.cu read it) -------
+// The "sync area" of every rank is one cudaMalloc'd block, IPC-mapped into all
+// peers:  flags first, then the SyncBN exchange slots.
+#define B200DP_XCHG_SLOTS 4
+#define B200DP_BN_MAX_CHUNKS 128                       /* 4096 ch / 32 (fp32 chunk) */
+#define B200DP_XCHG_FLOATS (2 * B200DP_BN_MAX_CHANNELS + B200DP_BN_MAX_CHUNKS)
+#define B200DP_BUCKET_FLAG_SLOTS 64
+
+struct b200dp_sync_area {
+  // SyncBN exchange: flag[slot][src_rank][chunk] = seq once that chunk of
+  // src_rank's vector for exchange `seq` has landed in data[slot][src_rank].
+  uint32_t bn_flag[B200DP_XCHG_SLOTS][B200DP_MAX_WORLD][B200DP_BN_MAX_CHUNKS];
+  // Gradient buckets: ready = "my bucket is packed", done = "I finished
+  // reading/writing everybody's slice".
+  uint32_t ready[B200DP_BUCKET_FLAG_SLOTS][B200DP_MAX_WORLD];
+  uint32_t done[B200DP_BUCKET_FLAG_SLOTS][B200DP_MAX_WORLD];
+  uint32_t barrier[B200DP_MAX_WORLD];
+  uint32_t error;  // set by a kernel whose flag wait timed out
+  uint32_t pad_[7];
+  uint32_t ticket[B200DP_BUCKET_FLAG_SLOTS];  // local "last CTA" elections (self-resetting)
+  float bn_data[B200DP_XCHG_SLOTS][B200DP_MAX_WORLD][B200DP_XCHG_FLOATS];
+};
+
+struct b200dp_comm {
+  int rank;
+  int world;
+  int device;
+  size_t heap_bytes;
+  void* heap[B200DP_MAX_WORLD];               // heap[rank] is the local allocation
+  b200dp_sync_area* sync[B200DP_MAX_WORLD];   // sync[rank] is the local one
+  bool peers_open;
+  uint32_t seq;
+};
+
+// Passed by value to kernels.
+struct b200dp_peers {
+  int rank;
+  int world;
+  b200dp_sync_area* sync[B200DP_MAX_WORLD];
+};
+
+static inline b200dp_peers b200dp_make_peers(const b200dp_comm* c) {
+  b200dp_peers p;
+  p.rank = c ? c->rank : 0;
+  p.world = c ? c->world : 1;
+  for (int i = 0; i < B200DP_MAX_WORLD; ++i) p.sync[i] = c ? c->sync[i] : nullptr;
+  return p;
+}

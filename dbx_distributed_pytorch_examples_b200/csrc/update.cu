@@ -1,0 +1,350 @@
+// update.cu — gradient bucket pack, and the all-reduce fused with the 1/N
+// average and the optimizer step, reading peer HBM directly over NVLink.
+//
+// Two-shot (large buckets):  rank r owns the r-th 1/world slice of the bucket.
+//   wait until every rank has raised `ready`            (grads are packed)
+//   for each 8-element unit of my slice:
+//       g  = sum over ranks, in rank order, of that unit read from the rank's
+//            bucket (ld.global.cg on the IPC-mapped pointer: an NVLink load)
+//       SGD-momentum / Adam on my master weights and state (local HBM, fp32)
+//       store the new parameters into EVERY rank's parameter buffer
+//   raise `done` on every rank, wait for every rank's `done`.
+// Bytes over NVLink per rank: (world-1)/world * S read + (world-1)/world * S_p
+// written — the reduce-scatter + all-gather minimum — and the optimizer pass
+// costs no extra trip through HBM for the gradient.
+// One-shot (small buckets): every rank reads all buckets and updates all of its
+// own parameters; nothing is pushed, (world-1)*S read.
+#include "common.cuh"
+
+namespace {
+
+using namespace b200dp;
+
+constexpr int kT = 512;
+constexpr int kPackMax = 112;  // tensors per pack launch (kernel parameter space)
+
+// ------------------------------- bucket pack -------------------------------
+struct PackTable {
+  const void* src[kPackMax];
+  long long numel[kPackMax];
+  long long off[kPackMax];
+  int n;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(kT) pack_kernel(const PackTable tab, T* __restrict__ dst,
+                                                  float scale) {
+  constexpr int N = Vec<T>::N;
+  const long long gtid = (long long)blockIdx.x * kT + threadIdx.x;
+  const long long gsz = (long long)gridDim.x * kT;
+  for (int t = 0; t < tab.n; ++t) {
+    const T* s = static_cast<const T*>(tab.src[t]);
+    T* d = dst + tab.off[t];
+    const long long n = tab.numel[t];
+    long long done = 0;
+    if (aligned16(s)) {
+      const long long nv = n / N;
+      for (long long i = gtid; i < nv; i += gsz) {
+        float f[N];
+        Vec<T>::unpack(ld_stream(s + i * N), f);
+#pragma unroll
+        for (int k = 0; k < N; ++k) f[k] *= scale;
+        *reinterpret_cast<uint4*>(d + i * N) = Vec<T>::pack(f);
+      }
+      done = nv * N;
+    }
+    for (long long i = done + gtid; i < n; i += gsz) d[i] = (T)((float)s[i] * scale);
+  }
+}
+
+// ---------------------------- fused reduce+update ---------------------------
+struct FusedArgs {
+  const void* grad[B200DP_MAX_WORLD];  // bucket base in every rank's heap
+  void* param[B200DP_MAX_WORLD];       // parameter base in every rank's heap
+  float* master;                       // local fp32 master, or NULL (PT == float)
+  float* s1;                           // momentum buffer / exp_avg
+  float* s2;                           // exp_avg_sq
+  long long begin, end;                // element range this rank reduces
+  b200dp_opt_args opt;
+  int one_shot;
+  int write_grads;
+  uint32_t seq;
+};
+
+template <typename T>
+__device__ __forceinline__ void load8(const T* p, float* f);
+template <>
+__device__ __forceinline__ void load8<float>(const float* p, float* f) {
+  Vec<float>::unpack(ld_cg(p), f);
+  Vec<float>::unpack(ld_cg(p + 4), f + 4);
+}
+template <>
+__device__ __forceinline__ void load8<__nv_bfloat16>(const __nv_bfloat16* p, float* f) {
+  Vec<__nv_bfloat16>::unpack(ld_cg(p), f);
+}
+template <typename T>
+__device__ __forceinline__ void store8(T* p, const float* f);
+template <>
+__device__ __forceinline__ void store8<float>(float* p, const float* f) {
+  *reinterpret_cast<uint4*>(p) = Vec<float>::pack(f);
+  *reinterpret_cast<uint4*>(p + 4) = Vec<float>::pack(f + 4);
+}
+template <>
+__device__ __forceinline__ void store8<__nv_bfloat16>(__nv_bfloat16* p, const float* f) {
+  *reinterpret_cast<uint4*>(p) = Vec<__nv_bfloat16>::pack(f);
+}
+
+// One optimizer step on 8 elements.  g: averaged gradient (in), p/s1/s2 in-out.
+// Operation order follows torch's foreach kernels so that fp32 results agree to
+// the last bit or two (TORCH/optim/sgd.py:322-380, TORCH/optim/adam.py:347+).
+template <int OPT>
+__device__ __forceinline__ void opt_step(const b200dp_opt_args& o, float* g, float* p, float* s1,
+                                         float* s2) {
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    float gk = g[k];
+    if (o.weight_decay != 0.f) gk = fmaf(p[k], o.weight_decay, gk);
+    if (OPT == B200DP_OPT_SGD) {
+      if (o.momentum != 0.f) {
+        float buf;
+        if (o.first_step) {
+          buf = gk;
+        } else {
+          buf = __fmul_rn(s1[k], o.momentum);
+          buf = fmaf(gk, 1.f - o.dampening, buf);
+        }
+        s1[k] = buf;
+        gk = o.nesterov ? fmaf(buf, o.momentum, gk) : buf;
+      }
+      p[k] = fmaf(gk, -o.lr, p[k]);
+    } else if (OPT == B200DP_OPT_ADAM) {
+      const float m = fmaf(1.f - o.beta1, gk - s1[k], s1[k]);  // lerp
+      float v = __fmul_rn(s2[k], o.beta2);
+      v = fmaf(__fmul_rn(1.f - o.beta2, gk), gk, v);           // addcmul
+      s1[k] = m;
+      s2[k] = v;
+      const float denom = __fdiv_rn(sqrtf(v), o.bias_correction2_sqrt) + o.eps;
+      p[k] = fmaf(__fdiv_rn(m, denom), -o.step_size, p[k]);
+    }
+  }
+}
+
+template <typename GT, typename PT, int OPT, int WORLD>
+__global__ void __launch_bounds__(kT, 1) fused_kernel(const FusedArgs A, b200dp_peers P) {
+  __shared__ bool is_last;
+  const int tid = threadIdx.x;
+  const int slot = A.seq % B200DP_BUCKET_FLAG_SLOTS;
+  b200dp_sync_area* me = P.sync[P.rank];
+  constexpr int world = WORLD;
+
+  if (world > 1) {
+    if (blockIdx.x == 0 && tid < world) st_release_sys(&P.sync[tid]->ready[slot][P.rank], A.seq);
+    if (tid < world) {
+      if (!wait_flag(&me->ready[slot][tid], A.seq)) atomicExch(&me->error, 1u);
+    }
+    __syncthreads();
+  }
+
+  const bool push = (world > 1) && !A.one_shot;
+  PT* my_param = static_cast<PT*>(A.param[P.rank]);
+  const long long gsz = (long long)gridDim.x * kT * 8;
+  for (long long i = A.begin + ((long long)blockIdx.x * kT + tid) * 8; i < A.end; i += gsz) {
+    // all ranks' loads are issued before the first add (WORLD is a constant,
+    // so this unrolls into WORLD independent NVLink requests per thread)
+    float g[8], h[WORLD > 1 ? WORLD - 1 : 1][8];
+    load8<GT>(static_cast<const GT*>(A.grad[0]) + i, g);
+#pragma unroll
+    for (int r = 1; r < world; ++r) load8<GT>(static_cast<const GT*>(A.grad[r]) + i, h[r - 1]);
+#pragma unroll
+    for (int r = 1; r < world; ++r) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[k] += h[r - 1][k];
+    }
+    if (A.write_grads) {
+      if (push) {
+#pragma unroll
+        for (int r = 0; r < world; ++r)
+          store8<GT>(static_cast<GT*>(const_cast<void*>(A.grad[r])) + i, g);
+      } else {
+        store8<GT>(static_cast<GT*>(const_cast<void*>(A.grad[P.rank])) + i, g);
+      }
+    }
+    if (OPT != B200DP_OPT_NONE) {
+      float p[8], s1[8], s2[8];
+      if (A.master) {
+        load8<float>(A.master + i, p);
+      } else {
+        load8<PT>(my_param + i, p);
+      }
+      if (OPT == B200DP_OPT_ADAM || (A.opt.momentum != 0.f && !A.opt.first_step))
+        load8<float>(A.s1 + i, s1);
+      if (OPT == B200DP_OPT_ADAM) load8<float>(A.s2 + i, s2);
+      opt_step<OPT>(A.opt, g, p, s1, s2);
+      if (A.master) store8<float>(A.master + i, p);
+      if (OPT == B200DP_OPT_ADAM || A.opt.momentum != 0.f) store8<float>(A.s1 + i, s1);
+      if (OPT == B200DP_OPT_ADAM) store8<float>(A.s2 + i, s2);
+      if (push) {
+#pragma unroll
+        for (int r = 0; r < world; ++r) store8<PT>(static_cast<PT*>(A.param[r]) + i, p);
+      } else {
+        store8<PT>(my_param + i, p);
+      }
+    }
+  }
+
+  if (world > 1) {
+    // all of this rank's peer stores are out before `done` is raised
+    __threadfence_system();
+    __syncthreads();
+    if (tid == 0) {
+      const unsigned int t = atomicAdd(&me->ticket[slot], 1u);
+      is_last = (t == gridDim.x - 1);
+      if (is_last) me->ticket[slot] = 0;
+    }
+    __syncthreads();
+    if (is_last && tid < world) {
+      __threadfence_system();
+      st_release_sys(&P.sync[tid]->done[slot][P.rank], A.seq);
+      if (!wait_flag(&me->done[slot][tid], A.seq)) atomicExch(&me->error, 1u);
+    }
+  }
+}
+
+template <typename GT, typename PT, int WORLD>
+int launch_fused_w(const FusedArgs& A, const b200dp_peers& P, int grid, cudaStream_t s) {
+  switch (A.opt.kind) {
+    case B200DP_OPT_NONE:
+      fused_kernel<GT, PT, B200DP_OPT_NONE, WORLD><<<grid, kT, 0, s>>>(A, P);
+      break;
+    case B200DP_OPT_SGD:
+      fused_kernel<GT, PT, B200DP_OPT_SGD, WORLD><<<grid, kT, 0, s>>>(A, P);
+      break;
+    case B200DP_OPT_ADAM:
+      fused_kernel<GT, PT, B200DP_OPT_ADAM, WORLD><<<grid, kT, 0, s>>>(A, P);
+      break;
+    default:
+      return B200DP_EINVAL;
+  }
+  B200DP_LAUNCH_CHECK();
+  return B200DP_OK;
+}
+
+template <typename GT, typename PT>
+int launch_fused(const FusedArgs& A, const b200dp_peers& P, int grid, cudaStream_t s) {
+  switch (P.world) {
+    case 1: return launch_fused_w<GT, PT, 1>(A, P, grid, s);
+    case 2: return launch_fused_w<GT, PT, 2>(A, P, grid, s);
+    case 4: return launch_fused_w<GT, PT, 4>(A, P, grid, s);
+    case 8: return launch_fused_w<GT, PT, 8>(A, P, grid, s);
+    default: return B200DP_EUNSUPPORTED;  // world sizes 1, 2, 4, 8 (one NVSwitch node)
+  }
+}
+
+}  // namespace
+
+extern "C" int b200dp_bucket_pack(const void* const* srcs, const int64_t* numels,
+                                  const int64_t* offsets, int n_tensors, void* dst, int dtype,
+                                  float scale, b200dp_stream_t stream) {
+  if (n_tensors < 0 || n_tensors > 1024) return B200DP_ETOOBIG;
+  if (n_tensors == 0) return B200DP_OK;
+  if (!srcs || !numels || !offsets || !dst) return B200DP_EINVAL;
+  if (dtype != B200DP_F32 && dtype != B200DP_BF16) return B200DP_EUNSUPPORTED;
+  if (!b200dp::aligned16(dst)) return B200DP_EALIGN;
+  cudaStream_t s = (cudaStream_t)stream;
+  for (int base = 0; base < n_tensors; base += kPackMax) {
+    PackTable tab;
+    tab.n = n_tensors - base < kPackMax ? n_tensors - base : kPackMax;
+    long long total = 0;
+    for (int t = 0; t < tab.n; ++t) {
+      if (numels[base + t] < 0 || offsets[base + t] < 0 || (offsets[base + t] & 7))
+        return B200DP_EINVAL;
+      if (numels[base + t] > 0 && !srcs[base + t]) return B200DP_EINVAL;
+      tab.src[t] = srcs[base + t];
+      tab.numel[t] = numels[base + t];
+      tab.off[t] = offsets[base + t];
+      total += numels[base + t];
+    }
+    long long want = (total / 8 + kT - 1) / kT;
+    int grid = (int)(want < 1 ? 1 : (want > 2 * B200DP_NUM_SMS ? 2 * B200DP_NUM_SMS : want));
+    if (dtype == B200DP_BF16)
+      pack_kernel<__nv_bfloat16><<<grid, kT, 0, s>>>(tab, static_cast<__nv_bfloat16*>(dst), scale);
+    else
+      pack_kernel<float><<<grid, kT, 0, s>>>(tab, static_cast<float*>(dst), scale);
+    B200DP_LAUNCH_CHECK();
+  }
+  return B200DP_OK;
+}
+
+extern "C" int b200dp_allreduce_update(b200dp_comm* comm, size_t grad_heap_off, int grad_dtype,
+                                       size_t param_heap_off, int param_dtype,
+                                       int64_t elem_offset, int64_t numel, float* master,
+                                       float* state1, float* state2, const b200dp_opt_args* opt,
+                                       int one_shot, int write_grads, int max_ctas, uint32_t seq,
+                                       b200dp_stream_t stream) {
+  if (!comm || !opt) return B200DP_EINVAL;
+  if (!comm->peers_open) return B200DP_ESTATE;
+  const int world = comm->world;
+  if (numel < 0 || elem_offset < 0 || (elem_offset & 7)) return B200DP_EINVAL;
+  if (numel % (8 * world) != 0) return B200DP_EINVAL;
+  if ((grad_dtype != B200DP_F32 && grad_dtype != B200DP_BF16) ||
+      (param_dtype != B200DP_F32 && param_dtype != B200DP_BF16))
+    return B200DP_EUNSUPPORTED;
+  if ((grad_heap_off & 15) || (param_heap_off & 15)) return B200DP_EALIGN;
+  const size_t gsz = grad_dtype == B200DP_BF16 ? 2 : 4, psz = param_dtype == B200DP_BF16 ? 2 : 4;
+  if (grad_heap_off + (size_t)(elem_offset + numel) * gsz > comm->heap_bytes) return B200DP_EINVAL;
+  if (world > 1 && seq == 0) return B200DP_EINVAL;
+  if (one_shot && write_grads && world > 1) return B200DP_EINVAL;
+  const int kind = opt->kind;
+  if (kind == B200DP_OPT_NONE) {
+    if (!write_grads) return B200DP_EINVAL;
+  } else {
+    if (param_heap_off + (size_t)(elem_offset + numel) * psz > comm->heap_bytes)
+      return B200DP_EINVAL;
+    if (param_dtype == B200DP_BF16 && !master) return B200DP_EINVAL;
+    if (kind == B200DP_OPT_ADAM && (!state1 || !state2)) return B200DP_EINVAL;
+    if (kind == B200DP_OPT_SGD && opt->momentum != 0.f && !state1) return B200DP_EINVAL;
+    if (!b200dp::aligned16(master) || !b200dp::aligned16(state1) || !b200dp::aligned16(state2))
+      return B200DP_EALIGN;
+  }
+  if (numel == 0) return B200DP_OK;
+
+  FusedArgs A;
+  for (int r = 0; r < B200DP_MAX_WORLD; ++r) {
+    A.grad[r] = nullptr;
+    A.param[r] = nullptr;
+  }
+  for (int r = 0; r < world; ++r) {
+    A.grad[r] = (const char*)comm->heap[r] + grad_heap_off + (size_t)elem_offset * gsz;
+    A.param[r] = (char*)comm->heap[r] + param_heap_off + (size_t)elem_offset * psz;
+  }
+  // master/state pointers address the first element of the bucket; the kernel
+  // indexes everything with the in-bucket element index.
+  A.master = master;
+  A.s1 = state1;
+  A.s2 = state2;
+  if (world > 1 && !one_shot) {
+    const long long slice = numel / world;
+    A.begin = slice * comm->rank;
+    A.end = A.begin + slice;
+  } else {
+    A.begin = 0;
+    A.end = numel;
+  }
+  A.opt = *opt;
+  A.one_shot = one_shot;
+  A.write_grads = write_grads;
+  A.seq = seq;
+
+  const long long units = (A.end - A.begin) / 8;
+  long long want = (units + kT - 1) / kT;
+  int cap = max_ctas > 0 ? max_ctas : (world > 1 ? 64 : B200DP_NUM_SMS);
+  if (cap > B200DP_NUM_SMS) cap = B200DP_NUM_SMS;  // every CTA must be resident: they elect a last one
+  int grid = (int)(want < 1 ? 1 : (want > cap ? cap : want));
+  const b200dp_peers P = b200dp_make_peers(comm);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (grad_dtype == B200DP_F32 && param_dtype == B200DP_F32)
+    return launch_fused<float, float>(A, P, grid, s);
+  if (grad_dtype == B200DP_BF16 && param_dtype == B200DP_BF16)
+    return launch_fused<__nv_bfloat16, __nv_bfloat16>(A, P, grid, s);
+  return B200DP_EUNSUPPORTED;  // gradient and parameter element types must match
+}

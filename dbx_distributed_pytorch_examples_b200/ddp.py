@@ -1,0 +1,467 @@
+"""DistributedDataParallel-compatible wrapper with a fused all-reduce + optimizer step.
+
+Drop-in for the call at 01_torch_distributor/01_basic_torch_distributor.py:291
+``DDP(model, device_ids=[local_rank], output_device=local_rank)`` and for the
+wrappers Accelerate / Ray build (04_accelerate/01_cifar_accelerate.ipynb:503,
+05_ray/02_cifar_resnet_pytorch_ray.ipynb:280).  What torch's Reducer + NCCL do
+per gradient bucket (TORCH/nn/parallel/distributed.py:330-2472,
+TORCH/include/torch/csrc/distributed/c10d/reducer.hpp:45-610) is done here by
+two kernels of csrc/update.cu per bucket: pack (grad -> flat bucket, x 1/N) and
+the fused reduce(+optimizer)(+parameter push) over NVLink peer memory.
+
+Layout.  Parameters of one dtype form an *arena*: a flat parameter buffer and a
+flat gradient buffer of the same length, both inside the communicator's
+peer-visible heap (every ``param.data`` is re-pointed to a view of the flat
+parameter buffer), plus — once an optimizer is fused — local fp32 state buffers
+and, for bf16 parameters, fp32 master weights.  Buckets are contiguous element
+ranges of an arena, filled in reverse registration order with torch's caps
+(first 1 MiB, then ``bucket_cap_mb``; distributed.py:831-853).
+
+Modes.
+* plain (default): after ``backward()`` every ``param.grad`` holds the gradient
+  averaged over the ranks, exactly what stock DDP leaves there, and the user's
+  optimizer runs as usual.
+* fused (``fuse_optimizer(optimizer)``): the bucket kernel also applies
+  SGD-momentum / Adam to this rank's 1/N slice and pushes the new parameters to
+  every rank; ``optimizer.step()`` only does the bookkeeping.  Precedent in
+  torch: ``_register_fused_optim`` (distributed.py:2097-2167).
+"""
+from __future__ import annotations
+
+import ctypes
+import math
+from contextlib import contextmanager
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+from torch.autograd import Variable
+from torch.nn.parallel import DistributedDataParallel
+
+from . import _lib
+from .comm import Communicator
+
+_ALIGN_ELEMS = 8
+_FIRST_BUCKET_BYTES = 1024 * 1024  # distributed.py:853 (_DEFAULT_FIRST_BUCKET_BYTES)
+
+
+def plan_buckets(numels: List[int], elem_size: int, world: int, cap_bytes: int,
+                 first_cap_bytes: int = _FIRST_BUCKET_BYTES):
+    """Lay parameters (already in bucket order) out in a flat arena.
+
+    Returns ``(offsets, buckets, total)``: the element offset of every parameter
+    (multiples of 8), ``buckets`` as ``(start, numel, first_param, last_param+1)``
+    with ``numel`` a multiple of ``8 * world`` (so that every rank's slice is
+    whole 16-byte vectors), and the arena length.  A bucket closes once it holds
+    at least its cap, like ``_compute_bucket_assignment_by_size``.
+    """
+    quantum = _ALIGN_ELEMS * world
+    offsets, buckets = [], []
+    cur, start, first = 0, 0, 0
+    cap = first_cap_bytes
+    for k, n in enumerate(numels):
+        offsets.append(cur)
+        cur += (n + _ALIGN_ELEMS - 1) // _ALIGN_ELEMS * _ALIGN_ELEMS
+        if (cur - start) * elem_size >= cap:
+            cur = start + (cur - start + quantum - 1) // quantum * quantum
+            buckets.append((start, cur - start, first, k + 1))
+            start, first, cap = cur, k + 1, cap_bytes
+    if first < len(numels):
+        cur = start + (cur - start + quantum - 1) // quantum * quantum
+        buckets.append((start, cur - start, first, len(numels)))
+    return offsets, buckets, cur
+
+
+class _Arena:
+    """All trainable parameters of one dtype."""
+
+    def __init__(self, dtype, params):
+        self.dtype = dtype
+        self.code = _lib.dtype_code(dtype)
+        self.esize = 2 if dtype == torch.bfloat16 else 4
+        self.params = params  # in bucket (reverse registration) order
+        self.offsets = self.buckets = None
+        self.total = 0
+        self.grad_off = self.param_off = 0  # byte offsets in the heap
+        self.flat_param = self.flat_grad = None
+        self.master = self.state1 = self.state2 = None
+        self.grad_views = []
+
+
+class _BucketState:
+    def __init__(self, arena, index, start, numel, p0, p1):
+        self.arena, self.index = arena, index
+        self.start, self.numel, self.p0, self.p1 = start, numel, p0, p1
+        n = p1 - p0
+        self.numels = (ctypes.c_int64 * n)(*[p.numel() for p in arena.params[p0:p1]])
+        self.offsets = (ctypes.c_int64 * n)(*[o - start for o in arena.offsets[p0:p1]])
+        self.srcs = (ctypes.c_void_p * n)()
+        self.pending = n
+        self.launched = False
+
+
+class _HookBucket:
+    """Duck-typed ``dist.GradBucket`` handed to hooks registered with
+    ``register_comm_hook`` (TORCH/include/torch/csrc/distributed/c10d/comm.hpp:20-100)."""
+
+    def __init__(self, b: _BucketState, last: bool):
+        self._b, self._last = b, last
+        a = b.arena
+        self._buf = a.flat_grad[b.start:b.start + b.numel]
+
+    def index(self):
+        return self._b.index
+
+    def buffer(self):
+        return self._buf
+
+    def set_buffer(self, t):
+        self._buf = t
+
+    def is_last(self):
+        return self._last
+
+    def parameters(self):
+        return list(self._b.arena.params[self._b.p0:self._b.p1])
+
+    def gradients(self):
+        return list(self._b.arena.grad_views[self._b.p0:self._b.p1])
+
+
+class B200DDP(DistributedDataParallel):
+    """``DistributedDataParallel``-compatible module wrapper (see module docstring).
+
+    Passes ``isinstance(m, torch.nn.parallel.DistributedDataParallel)`` (the Ray
+    example checks it, 05_ray/02_cifar_resnet_pytorch_ray.ipynb:317) and exposes
+    ``.module``; none of torch's Reducer machinery is constructed.
+    """
+
+    def __init__(self, module, device_ids=None, output_device=None, dim=0, broadcast_buffers=True,
+                 init_sync=True, process_group=None, bucket_cap_mb=None, find_unused_parameters=False,
+                 check_reduction=False, gradient_as_bucket_view=False, static_graph=False,
+                 delay_all_reduce_named_params=None, param_to_hook_all_reduce=None,
+                 mixed_precision=None, device_mesh=None, skip_all_reduce_unused_params=False, *,
+                 one_shot_bytes: int = 256 * 1024, max_ctas: int = 48):
+        torch.nn.Module.__init__(self)
+        if mixed_precision is not None or device_mesh is not None or delay_all_reduce_named_params is not None:
+            raise NotImplementedError("B200DDP does not implement mixed_precision / device_mesh / delayed all-reduce")
+        params = [p for p in module.parameters() if p.requires_grad]
+        if not params:
+            # same condition and exception type as distributed.py:737-745
+            raise RuntimeError("DistributedDataParallel is not needed when a module doesn't have any "
+                               "parameter that requires a gradient.")
+        if device_ids is not None and len(device_ids) > 1:
+            raise ValueError("device_ids can only be None or contain a single element.")  # distributed.py:747-751
+        devices = {p.device for p in params}
+        if len(devices) != 1 or next(iter(devices)).type != "cuda":
+            raise ValueError("B200DDP needs all parameters on one CUDA device; it has no CPU path "
+                             f"(found {sorted(str(d) for d in devices)})")
+        self.device = next(iter(devices))
+        self.module = module
+        self.dim = dim
+        self.device_ids = [self.device.index]
+        self.output_device = self.device.index if output_device is None else output_device
+        self.broadcast_buffers = broadcast_buffers
+        self.find_unused_parameters = find_unused_parameters
+        self.static_graph = static_graph
+        self.gradient_as_bucket_view = True  # by construction
+        self.require_backward_grad_sync = True
+        self.require_forward_param_sync = True
+        self.process_group = process_group
+        self.one_shot_bytes = int(one_shot_bytes)
+        self.max_ctas = int(max_ctas)
+        self.materialize_grads = True
+        self._optimizer = None
+        self._opt_step_count = 0
+        self._comm_hook = None
+        self._iteration_armed = False
+        self.bucket_bytes_cap = int((25 if bucket_cap_mb is None else bucket_cap_mb) * 1024 * 1024)
+
+        if dist.is_available() and dist.is_initialized():
+            self.world = dist.get_world_size(process_group)
+            self.rank = dist.get_rank(process_group)
+        else:
+            self.world, self.rank = 1, 0
+
+        # ---- arenas, buckets, heap -------------------------------------------------
+        by_dtype = {}
+        for p in reversed(params):  # reverse registration order ~ gradient-ready order
+            by_dtype.setdefault(p.dtype, []).append(p)
+        self._arenas = [_Arena(dt, ps) for dt, ps in by_dtype.items()]
+        heap = 0
+        for a in self._arenas:
+            a.offsets, a.buckets, a.total = plan_buckets([p.numel() for p in a.params], a.esize, self.world,
+                                                         self.bucket_bytes_cap)
+            nbytes = (a.total * a.esize + 511) // 512 * 512
+            a.grad_off, a.param_off = heap, heap + nbytes
+            heap += 2 * nbytes
+        with torch.cuda.device(self.device):
+            self.comm = Communicator(process_group, heap_bytes=heap, device=self.device)
+            self._comm_stream = torch.cuda.Stream(device=self.device)
+        self._param_index = {}
+        self._buckets: List[_BucketState] = []
+        with torch.no_grad():
+            for a in self._arenas:
+                a.flat_grad = self.comm.heap_view(a.grad_off, a.total, a.dtype)
+                a.flat_param = self.comm.heap_view(a.param_off, a.total, a.dtype)
+                for p, off in zip(a.params, a.offsets):
+                    view = a.flat_param[off:off + p.numel()].view(p.shape)
+                    view.copy_(p.data)
+                    p.data = view
+                    a.grad_views.append(a.flat_grad[off:off + p.numel()].view(p.shape))
+                for (start, numel, p0, p1) in a.buckets:
+                    b = _BucketState(a, len(self._buckets), start, numel, p0, p1)
+                    self._buckets.append(b)
+                    for k in range(p0, p1):
+                        self._param_index[a.params[k]] = (b, k - p0, a.grad_views[k])
+        if self.world > 1 and init_sync:
+            self._sync_module_states()
+        for p in params:
+            p.register_post_accumulate_grad_hook(self._on_grad_ready)
+        # checkpoints must not drag the whole heap along: hand out copies
+        module._register_state_dict_hook(_clone_state_dict_hook)
+        torch.cuda.synchronize(self.device)
+        if self.world > 1:
+            self.comm.barrier()
+
+    # ---- init-time synchronisation (distributed.py:879-890) -------------------------
+    def _sync_module_states(self):
+        for a in self._arenas:
+            dist.broadcast(a.flat_param, src=dist.get_global_rank(self.process_group, 0)
+                           if self.process_group is not None else 0, group=self.process_group)
+        for buf in self.module.buffers():
+            dist.broadcast(buf, src=dist.get_global_rank(self.process_group, 0)
+                           if self.process_group is not None else 0, group=self.process_group)
+
+    def _needs_buffer_broadcast(self):
+        from .syncbn import B200SyncBatchNorm
+
+        owned = set()
+        for m in self.module.modules():
+            if isinstance(m, B200SyncBatchNorm):
+                owned.update(id(b) for b in m.buffers(recurse=False))
+        return [b for b in self.module.buffers() if id(b) not in owned]
+
+    # ---- forward ---------------------------------------------------------------------
+    def forward(self, *inputs, **kwargs):
+        if self.world > 1 and self.broadcast_buffers and self.require_forward_param_sync:
+            # buffers of B200SyncBatchNorm layers are identical on all ranks by construction
+            for buf in self._needs_buffer_broadcast():
+                dist.broadcast(buf, src=0, group=self.process_group)
+        if torch.is_grad_enabled() and self.require_backward_grad_sync:
+            self._arm_iteration()
+        return self.module(*inputs, **kwargs)
+
+    def _arm_iteration(self):
+        for b in self._buckets:
+            b.pending = b.p1 - b.p0
+            b.launched = False
+        self._next_bucket = 0
+        self._callback_queued = False
+        self._iteration_armed = True
+        # one sequence number per bucket, reserved up front so that it does not
+        # depend on the order in which gradients become ready
+        self._seqs = [self.comm.next_seq() for _ in self._buckets]
+        if self._optimizer is not None:
+            self._opt_step_count += 1
+
+    @contextmanager
+    def no_sync(self):
+        """Accumulate gradients locally (distributed.py:1474-1500)."""
+        old = self.require_backward_grad_sync
+        self.require_backward_grad_sync = False
+        try:
+            yield
+        finally:
+            self.require_backward_grad_sync = old
+
+    # ---- backward hooks ----------------------------------------------------------------
+    def _on_grad_ready(self, param):
+        if not (self.require_backward_grad_sync and self._iteration_armed):
+            return
+        if not self._callback_queued:
+            Variable._execution_engine.queue_callback(self._finalize_backward)
+            self._callback_queued = True
+        b, _, _ = self._param_index[param]
+        b.pending -= 1
+        while self._next_bucket < len(self._buckets):
+            nb = self._buckets[self._next_bucket]
+            if nb.pending > 0:
+                break
+            self._launch_bucket(nb)
+            self._next_bucket += 1
+
+    def _finalize_backward(self):
+        # buckets with parameters that received no gradient this iteration
+        while self._next_bucket < len(self._buckets):
+            self._launch_bucket(self._buckets[self._next_bucket])
+            self._next_bucket += 1
+        torch.cuda.current_stream(self.device).wait_stream(self._comm_stream)
+        self._iteration_armed = False
+
+    def _launch_bucket(self, b: _BucketState):
+        lib = _lib.lib()
+        a = b.arena
+        cur = torch.cuda.current_stream(self.device)
+        self._comm_stream.wait_stream(cur)
+        with torch.cuda.stream(self._comm_stream):
+            stream = self._comm_stream.cuda_stream
+            n = 0
+            for k in range(b.p0, b.p1):
+                p = a.params[k]
+                g = p.grad
+                if g is None:
+                    a.grad_views[k].zero_()
+                    continue
+                if g.dtype != a.dtype or not g.is_contiguous():
+                    g = g.to(a.dtype).contiguous()
+                g.record_stream(self._comm_stream)
+                b.srcs[n] = g.data_ptr()
+                b.numels[n] = p.numel()
+                b.offsets[n] = a.offsets[k] - b.start
+                n += 1
+            bucket_ptr = a.flat_grad.data_ptr() + b.start * a.esize
+            _lib.check(lib.b200dp_bucket_pack(b.srcs, b.numels, b.offsets, n, bucket_ptr, a.code,
+                                              1.0 / self.world, stream), "b200dp_bucket_pack")
+            if self._comm_hook is not None:
+                self._run_comm_hook(b)
+            else:
+                opt = self._opt_args(a)
+                fused = opt.kind != _lib.OPT_NONE
+                write_grads = 1 if (self.materialize_grads or not fused) else 0
+                one_shot = int(self.world > 1 and not write_grads and b.numel * a.esize <= self.one_shot_bytes)
+                off = b.start
+                _lib.check(lib.b200dp_allreduce_update(
+                    self.comm.handle, a.grad_off, a.code, a.param_off, a.code, off, b.numel,
+                    None if a.master is None else a.master.data_ptr() + 4 * off,
+                    None if a.state1 is None else a.state1.data_ptr() + 4 * off,
+                    None if a.state2 is None else a.state2.data_ptr() + 4 * off,
+                    ctypes.byref(opt), one_shot, write_grads, self.max_ctas,
+                    self._seqs[b.index], stream), "b200dp_allreduce_update")
+        keep = self.materialize_grads or self._optimizer is None or self._comm_hook is not None
+        for k in range(b.p0, b.p1):
+            a.params[k].grad = a.grad_views[k] if keep else None
+        b.launched = True
+
+    # ---- comm hook compatibility (distributed.py:1987) -----------------------------------
+    def register_comm_hook(self, state, hook):
+        if not callable(hook):
+            raise TypeError("Communication hook must be callable.")
+        if self._optimizer is not None:
+            raise RuntimeError("a comm hook cannot be combined with a fused optimizer")
+        self._comm_hook = (state, hook)
+
+    def _run_comm_hook(self, b: _BucketState):
+        state, hook = self._comm_hook
+        hb = _HookBucket(b, b.index == len(self._buckets) - 1)
+        # the pack kernel pre-divided by world like the Reducer does; hooks such as
+        # default_hooks.allreduce_hook divide themselves, so undo it
+        hb.buffer().mul_(self.world)
+        fut = hook(state, hb)
+        out = fut.wait() if hasattr(fut, "wait") else fut
+        if isinstance(out, (list, tuple)):
+            out = out[0]
+        if out.data_ptr() != hb._b.arena.flat_grad.data_ptr() + b.start * b.arena.esize:
+            b.arena.flat_grad[b.start:b.start + b.numel].copy_(out.view(-1)[:b.numel])
+
+    # ---- fused optimizer -----------------------------------------------------------------
+    def fuse_optimizer(self, optimizer, materialize_grads: bool = False):
+        """Move ``optimizer``'s update into the bucket kernels.
+
+        Supports ``torch.optim.SGD`` (momentum, dampening, nesterov, weight_decay;
+        01_basic_torch_distributor.py:294) and ``torch.optim.Adam`` (coupled L2
+        weight decay; 02_cifar_torch_distributor_resnet.py:213,
+        04_accelerate/01_cifar_accelerate.ipynb:482-486), one set of
+        hyper-parameters for all wrapped parameters.  Hyper-parameters are read
+        from ``optimizer.param_groups`` at every step, so LR schedulers keep
+        working.  ``optimizer.step()`` becomes bookkeeping only.
+        """
+        if self._comm_hook is not None:
+            raise RuntimeError("a fused optimizer cannot be combined with a comm hook")
+        if isinstance(optimizer, torch.optim.Adam) and not isinstance(optimizer, torch.optim.AdamW):
+            kind = _lib.OPT_ADAM
+            if any(g.get("amsgrad") or g.get("maximize") for g in optimizer.param_groups):
+                raise NotImplementedError("amsgrad / maximize are not fused")
+        elif isinstance(optimizer, torch.optim.SGD):
+            kind = _lib.OPT_SGD
+            if any(g.get("maximize") for g in optimizer.param_groups):
+                raise NotImplementedError("maximize is not fused")
+        else:
+            raise NotImplementedError(f"cannot fuse {type(optimizer).__name__}; use SGD or Adam")
+        ours = set(self._param_index)
+        groups = [g for g in optimizer.param_groups if any(p in ours for p in g["params"])]
+        covered = {p for g in groups for p in g["params"]}
+        if not ours <= covered:
+            raise ValueError("the optimizer does not hold all parameters of the wrapped module")
+        keys = ("lr", "momentum", "dampening", "nesterov", "weight_decay", "betas", "eps")
+        first = {k: groups[0].get(k) for k in keys}
+        for g in groups[1:]:
+            if {k: g.get(k) for k in keys} != first:
+                raise NotImplementedError("parameter groups with different hyper-parameters are not fused")
+        self._optimizer, self._opt_kind, self._opt_group = optimizer, kind, groups[0]
+        self.materialize_grads = bool(materialize_grads)
+        self._opt_step_count = 0
+        for a in self._arenas:
+            a.state1 = torch.zeros(a.total, dtype=torch.float32, device=self.device)
+            a.state2 = torch.zeros(a.total, dtype=torch.float32, device=self.device) if kind == _lib.OPT_ADAM else None
+            a.master = a.flat_param.float() if a.dtype != torch.float32 else None
+            for p, off in zip(a.params, a.offsets):
+                st = optimizer.state[p]
+                if kind == _lib.OPT_SGD:
+                    st["momentum_buffer"] = a.state1[off:off + p.numel()].view(p.shape)
+                else:
+                    st["step"] = torch.tensor(0.0)
+                    st["exp_avg"] = a.state1[off:off + p.numel()].view(p.shape)
+                    st["exp_avg_sq"] = a.state2[off:off + p.numel()].view(p.shape)
+        ddp = self
+
+        def step(closure=None):
+            loss = closure() if closure is not None else None
+            if ddp._opt_kind == _lib.OPT_ADAM:
+                for a in ddp._arenas:
+                    for p in a.params:
+                        optimizer.state[p]["step"] += 1
+            return loss
+
+        optimizer.step = step
+        return optimizer
+
+    def _opt_args(self, arena) -> _lib.OptArgs:
+        o = _lib.OptArgs()
+        if self._optimizer is None:
+            o.kind = _lib.OPT_NONE
+            return o
+        g = self._opt_group
+        o.kind = self._opt_kind
+        o.lr = float(g["lr"])
+        o.weight_decay = float(g.get("weight_decay", 0.0))
+        t = self._opt_step_count
+        if self._opt_kind == _lib.OPT_SGD:
+            o.momentum = float(g.get("momentum", 0.0))
+            o.dampening = float(g.get("dampening", 0.0))
+            o.nesterov = int(bool(g.get("nesterov", False)))
+            o.first_step = int(t == 1)
+        else:
+            b1, b2 = g["betas"]
+            o.beta1, o.beta2, o.eps = float(b1), float(b2), float(g["eps"])
+            # computed in double on the host, like _single_tensor_adam (adam.py)
+            o.step_size = float(g["lr"]) / (1.0 - b1 ** t)
+            o.bias_correction2_sqrt = math.sqrt(1.0 - b2 ** t)
+        return o
+
+    # ---- housekeeping ---------------------------------------------------------------------
+    def bucket_sizes_bytes(self):
+        return [b.numel * b.arena.esize for b in self._buckets]
+
+    def __getstate__(self):
+        raise NotImplementedError("pickle module.state_dict() (or .module) instead of the B200DDP wrapper")
+
+    def _get_ddp_logging_data(self):
+        return {"backend_name": "b200dp-nvlink-p2p", "world_size": self.world, "rank": self.rank}
+
+
+def _clone_state_dict_hook(module, state_dict, prefix, local_metadata):
+    for k, v in list(state_dict.items()):
+        if isinstance(v, torch.Tensor) and v.is_cuda:
+            state_dict[k] = v.detach().clone()
+    return state_dict

@@ -1,0 +1,292 @@
+"""SyncBatchNorm replacement with fused (+residual)+ReLU epilogues, NHWC.
+
+Drop-in for ``torch.nn.SyncBatchNorm`` (TORCH/nn/modules/batchnorm.py:615-905):
+same constructor, ``convert_sync_batchnorm`` classmethod, state_dict keys
+(``weight, bias, running_mean, running_var, num_batches_tracked``) and error
+behaviour.  It replaces the ``nn.BatchNorm2d`` layers of the reference models
+(setup/resnet18.py:8,12,19,35; torchvision resnet18/50 used at
+01_torch_distributor/02_cifar_torch_distributor_resnet.py:146 and
+03_tiny_imagenet_torch_distributor_resnet.py:130) and, with ``fuse_relu`` /
+``forward(x, residual)``, also the ReLU and skip-add that follow them
+(setup/resnet18.py:23-26,57).
+
+Forward = two kernels (Welford statistics + exchange; merge + normalise),
+backward = two kernels (reduce + exchange; sum + apply) — see csrc/bn.cu.  The
+oracle of the arithmetic is TORCH/nn/modules/_functions.py:7-209.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+from torch.nn.modules.batchnorm import _BatchNorm
+
+from . import _lib
+from .comm import stats_communicator
+
+_scratch = {}
+
+
+def _bn_scratch(device: torch.device) -> torch.Tensor:
+    """Zero-filled reduction scratch, one per (device, stream): calls that share
+    it are ordered by that stream."""
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    buf = _scratch.get(key)
+    if buf is None:
+        nbytes = int(_lib.lib().b200dp_bn_scratch_bytes(0))
+        buf = torch.zeros(nbytes, dtype=torch.uint8, device=device)
+        _scratch[key] = buf
+    return buf
+
+
+def _as_rows(x: torch.Tensor) -> torch.Tensor:
+    """Return x laid out so that its memory is [M, C] row-major (channels last)."""
+    if x.dim() == 2:
+        return x.contiguous()
+    if x.dim() == 4:
+        return x.contiguous(memory_format=torch.channels_last)
+    if x.dim() == 5:
+        return x.contiguous(memory_format=torch.channels_last_3d)
+    if x.dim() == 3:  # [N, C, L]: view as [N, C, L, 1]
+        return x.unsqueeze(-1).contiguous(memory_format=torch.channels_last).squeeze(-1)
+    raise ValueError(f"expected at least 2D input (got {x.dim()}D input)")
+
+
+class _FusedSyncBN(torch.autograd.Function):
+    """y = act(bn(x) [+ residual]) with batch statistics shared across ranks."""
+
+    @staticmethod
+    def forward(ctx, x, residual, weight, bias, running_mean, running_var, eps, momentum, relu, comm):
+        lib = _lib.lib()
+        x = _as_rows(x)
+        C = x.shape[1]
+        M = x.numel() // C
+        world = comm.world if comm is not None else 1
+        if M == 1 and world < 2:
+            raise ValueError(f"Expected more than 1 value per channel when training, got input size {M}")
+        dt = _lib.dtype_code(x.dtype)
+        if residual is not None:
+            if residual.shape != x.shape or residual.dtype != x.dtype:
+                raise ValueError("residual must have the shape and dtype of the input")
+            residual = _as_rows(residual)
+        w32 = None if weight is None else weight.detach().float().contiguous()
+        b32 = None if bias is None else bias.detach().float().contiguous()
+        dev = x.device
+        with torch.cuda.device(dev):
+            stream = _lib.current_stream()
+            scratch = _bn_scratch(dev)
+            stats = torch.empty(2 * C + 1, dtype=torch.float32, device=dev)
+            save = torch.empty(2 * C + 1, dtype=torch.float32, device=dev)  # mean | invstd | count
+            y = torch.empty_like(x)
+            h = comm.handle if world > 1 else None
+            seq = comm.next_seq() if world > 1 else 0
+            _lib.check(lib.b200dp_bn_fwd_stats(x.data_ptr(), dt, M, C, scratch.data_ptr(), stats.data_ptr(),
+                                               h, seq, stream), "b200dp_bn_fwd_stats")
+            _lib.check(lib.b200dp_bn_fwd_apply(
+                x.data_ptr(), _lib.ptr(residual), y.data_ptr(), dt, M, C, stats.data_ptr(),
+                _lib.ptr(w32), _lib.ptr(b32), float(eps), float(momentum),
+                _lib.ptr(running_mean), _lib.ptr(running_var),
+                save.data_ptr(), save.data_ptr() + 4 * C, save.data_ptr() + 8 * C,
+                int(bool(relu)), h, seq, stream), "b200dp_bn_fwd_apply")
+        # ReLU mask in the backward: recomputed from x when nothing was added,
+        # otherwise taken from the saved output.
+        ctx.relu_mode = 0 if not relu else (1 if residual is None else 2)
+        ctx.comm = comm
+        ctx.dims = (M, C, dt)
+        ctx.has_residual = residual is not None
+        ctx.save_for_backward(x, y if ctx.relu_mode == 2 else None, weight, bias, w32, b32, save)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        lib = _lib.lib()
+        x, y, weight, bias, w32, b32, save = ctx.saved_tensors
+        M, C, dt = ctx.dims
+        comm = ctx.comm
+        world = comm.world if comm is not None else 1
+        if dy.dtype != x.dtype:
+            dy = dy.to(x.dtype)
+        dy = _as_rows(dy)
+        dev = x.device
+        with torch.cuda.device(dev):
+            stream = _lib.current_stream()
+            scratch = _bn_scratch(dev)
+            sums = torch.empty(2 * C, dtype=torch.float32, device=dev)
+            gw = torch.empty(C, dtype=torch.float32, device=dev) if weight is not None else None
+            gb = torch.empty(C, dtype=torch.float32, device=dev) if bias is not None else None
+            dx = torch.empty_like(x)
+            dres = torch.empty_like(x) if (ctx.has_residual and ctx.needs_input_grad[1]) else None
+            h = comm.handle if world > 1 else None
+            seq = comm.next_seq() if world > 1 else 0
+            mean_p, invstd_p, count_p = save.data_ptr(), save.data_ptr() + 4 * C, save.data_ptr() + 8 * C
+            _lib.check(lib.b200dp_bn_bwd_reduce(
+                dy.data_ptr(), x.data_ptr(), _lib.ptr(y), dt, M, C, mean_p, invstd_p,
+                _lib.ptr(w32), _lib.ptr(b32), ctx.relu_mode, scratch.data_ptr(), sums.data_ptr(),
+                _lib.ptr(gw), _lib.ptr(gb), h, seq, stream), "b200dp_bn_bwd_reduce")
+            _lib.check(lib.b200dp_bn_bwd_apply(
+                dy.data_ptr(), x.data_ptr(), _lib.ptr(y), dx.data_ptr(), _lib.ptr(dres), dt, M, C,
+                mean_p, invstd_p, _lib.ptr(w32), _lib.ptr(b32), sums.data_ptr(), count_p,
+                ctx.relu_mode, h, seq, stream), "b200dp_bn_bwd_apply")
+        if gw is not None and weight.dtype != torch.float32:
+            gw = gw.to(weight.dtype)
+        if gb is not None and bias.dtype != torch.float32:
+            gb = gb.to(bias.dtype)
+        if not ctx.needs_input_grad[2]:
+            gw = None
+        if not ctx.needs_input_grad[3]:
+            gb = None
+        return dx, dres, gw, gb, None, None, None, None, None, None
+
+
+class _FusedBNInference(torch.autograd.Function):
+    """Eval-mode y = act(bn(x; running stats) [+ residual])."""
+
+    @staticmethod
+    def forward(ctx, x, residual, weight, bias, running_mean, running_var, eps, relu):
+        lib = _lib.lib()
+        x = _as_rows(x)
+        C = x.shape[1]
+        M = x.numel() // C
+        dt = _lib.dtype_code(x.dtype)
+        if residual is not None:
+            residual = _as_rows(residual)
+        w32 = None if weight is None else weight.detach().float().contiguous()
+        b32 = None if bias is None else bias.detach().float().contiguous()
+        rm, rv = running_mean.float().contiguous(), running_var.float().contiguous()
+        y = torch.empty_like(x)
+        with torch.cuda.device(x.device):
+            _lib.check(lib.b200dp_bn_inference(x.data_ptr(), _lib.ptr(residual), y.data_ptr(), dt, M, C,
+                                               rm.data_ptr(), rv.data_ptr(), _lib.ptr(w32), _lib.ptr(b32),
+                                               float(eps), int(bool(relu)), _lib.current_stream()),
+                       "b200dp_bn_inference")
+        ctx.relu = bool(relu)
+        ctx.eps = float(eps)
+        ctx.has_residual = residual is not None
+        ctx.save_for_backward(x, y, w32, rm, rv)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        # Frozen statistics: the layer is an affine map per channel (not on the
+        # training hot path; plain tensor algebra on the GPU).
+        x, y, w32, rm, rv = ctx.saved_tensors
+        shape = [1, -1] + [1] * (x.dim() - 2)
+        g = dy * (y > 0) if ctx.relu else dy
+        invstd = torch.rsqrt(rv + ctx.eps)
+        scale = invstd if w32 is None else invstd * w32
+        dx = (g.float() * scale.view(shape)).to(x.dtype)
+        red = [d for d in range(x.dim()) if d != 1]
+        gw = (g.float() * (x.float() - rm.view(shape)) * invstd.view(shape)).sum(red) if w32 is not None else None
+        gb = g.float().sum(red) if w32 is not None else None
+        return dx, (g if ctx.has_residual else None), gw, gb, None, None, None, None
+
+
+class B200SyncBatchNorm(_BatchNorm):
+    """``nn.SyncBatchNorm`` with optional fused ReLU and residual add.
+
+    ``forward(input, residual=None)`` returns ``act(bn(input) + residual)`` where
+    ``act`` is ReLU when ``fuse_relu`` is set.  Parameters, running statistics
+    and all arithmetic of the statistics stay float32 whatever the activation
+    dtype (float32 or bfloat16).
+    """
+
+    def __init__(self, num_features: int, eps: float = 1e-5, momentum: Optional[float] = 0.1,
+                 affine: bool = True, track_running_stats: bool = True, process_group=None,
+                 device=None, dtype=None, fuse_relu: bool = False) -> None:
+        super().__init__(num_features, eps, momentum, affine, track_running_stats,
+                         device=device, dtype=dtype)
+        self.process_group = process_group
+        self.fuse_relu = fuse_relu
+
+    def _apply(self, fn, recurse=True):
+        # keep statistics and affine parameters in float32 through .to(bf16)/.half()
+        super()._apply(fn, recurse)
+        for name, p in list(self._parameters.items()):
+            if p is not None and p.is_floating_point() and p.dtype != torch.float32:
+                p.data = p.data.float()
+                if p.grad is not None:
+                    p.grad.data = p.grad.data.float()
+        for name, b in list(self._buffers.items()):
+            if b is not None and b.is_floating_point() and b.dtype != torch.float32:
+                self._buffers[name] = b.float()
+        return self
+
+    def _check_input_dim(self, input):
+        if input.dim() < 2:
+            raise ValueError(f"expected at least 2D input (got {input.dim()}D input)")
+
+    def _check_non_zero_input_channels(self, input):
+        if input.size(1) == 0:
+            raise ValueError("SyncBatchNorm number of input channels should be non-zero")
+
+    def extra_repr(self):
+        return super().extra_repr() + f", fuse_relu={self.fuse_relu}"
+
+    def forward(self, input: torch.Tensor, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+        self._check_input_dim(input)
+        self._check_non_zero_input_channels(input)
+        if not input.is_cuda:
+            # same condition as TORCH/nn/modules/batchnorm.py:800-809; there is no CPU path here
+            raise ValueError("SyncBatchNorm expected input tensor to be on GPU or "
+                             f"{torch._C._get_privateuse1_backend_name()}")
+
+        # exponential_average_factor exactly as _BatchNorm / SyncBatchNorm choose it
+        if self.momentum is None:
+            factor = 0.0
+        else:
+            factor = self.momentum
+        if self.training and self.track_running_stats:
+            self.num_batches_tracked.add_(1)
+            if self.momentum is None:
+                factor = 1.0 / self.num_batches_tracked.item()
+            else:
+                factor = self.momentum
+
+        bn_training = self.training or (self.running_mean is None and self.running_var is None)
+        running_mean = self.running_mean if not self.training or self.track_running_stats else None
+        running_var = self.running_var if not self.training or self.track_running_stats else None
+
+        if not bn_training:
+            return _FusedBNInference.apply(input, residual, self.weight, self.bias, running_mean,
+                                           running_var, self.eps, self.fuse_relu)
+
+        comm = None
+        if self.training and dist.is_available() and dist.is_initialized():
+            world = dist.get_world_size(self.process_group)
+            if world > 1:
+                comm = stats_communicator(self.process_group)
+        return _FusedSyncBN.apply(input, residual, self.weight, self.bias, running_mean, running_var,
+                                  self.eps, factor, self.fuse_relu, comm)
+
+    @classmethod
+    def convert_sync_batchnorm(cls, module, process_group=None):
+        """Replace every ``_BatchNorm`` (and ``nn.SyncBatchNorm``) under ``module``.
+
+        Mirrors ``nn.SyncBatchNorm.convert_sync_batchnorm``
+        (TORCH/nn/modules/batchnorm.py:844-905): the new layer shares the source
+        layer's Parameters and buffers; children are converted recursively.
+        """
+        out = module
+        if isinstance(module, _BatchNorm) and not isinstance(module, cls):
+            out = cls(module.num_features, module.eps, module.momentum, module.affine,
+                      module.track_running_stats,
+                      process_group if process_group is not None else getattr(module, "process_group", None))
+            if module.affine:
+                with torch.no_grad():
+                    out.weight = module.weight
+                    out.bias = module.bias
+            out.running_mean = module.running_mean
+            out.running_var = module.running_var
+            out.num_batches_tracked = module.num_batches_tracked
+            out.training = module.training
+            if hasattr(module, "qconfig"):
+                out.qconfig = module.qconfig
+            out._apply(lambda t: t)  # statistics / affine back to float32 if the source was cast
+        for name, child in module.named_children():
+            out.add_module(name, cls.convert_sync_batchnorm(child, process_group))
+        del module
+        return out
+
+
+convert_sync_batchnorm = B200SyncBatchNorm.convert_sync_batchnorm
