@@ -67,6 +67,39 @@ def build(force: bool = False, verbose: bool = False) -> str:
 _lock = threading.Lock()
 _lib = None
 
+# ---- launch accounting -----------------------------------------------------------
+# CALLS counts every entry-point call (bench.py reports the kernel launches of a timed
+# region from it).  PROFILER, when set, brackets each call with CUDA events on the
+# stream the call was given (bench.py's per-kernel roofline pass).
+CALLS = {}
+PROFILER = None
+_COMPUTE = ("b200dp_augment_u8_bf16", "b200dp_bn_fwd_stats", "b200dp_bn_fwd_apply", "b200dp_bn_inference",
+            "b200dp_bn_bwd_reduce", "b200dp_bn_bwd_apply", "b200dp_bucket_pack", "b200dp_allreduce_update",
+            "b200dp_comm_barrier")
+
+
+class _Entry:
+    __slots__ = ("name", "fn")
+
+    def __init__(self, name, fn):
+        self.name, self.fn = name, fn
+
+    def __call__(self, *args):
+        CALLS[self.name] = CALLS.get(self.name, 0) + 1
+        if PROFILER is None:
+            return self.fn(*args)
+        return PROFILER(self.name, self.fn, args)
+
+
+class _Handle:
+    """Attribute access like a CDLL; compute entry points go through _Entry."""
+
+    def __init__(self, cdll):
+        for name in _SIGNATURES:
+            fn = getattr(cdll, name)
+            setattr(self, name, _Entry(name, fn) if name in _COMPUTE else fn)
+        self._cdll = cdll
+
 _VP = c_void_p
 _SIGNATURES = {
     # name: (restype, argtypes)
@@ -108,7 +141,7 @@ def exported_symbols():
     return sorted(_SIGNATURES)
 
 
-def lib() -> ctypes.CDLL:
+def lib():
     """Load libb200dp.so once; raise if it has not been built."""
     global _lib
     if _lib is not None:
@@ -124,7 +157,7 @@ def lib() -> ctypes.CDLL:
                 fn = getattr(handle, name)  # AttributeError if the symbol is not exported
                 fn.restype = res
                 fn.argtypes = args
-            _lib = handle
+            _lib = _Handle(handle)
     return _lib
 
 

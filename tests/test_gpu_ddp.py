@@ -1,0 +1,114 @@
+"""GPU, one rank: the DDP wrapper end to end on the reference's ResNet-18 against stock
+torch (same seeds): averaged gradients, fused SGD / Adam updates, drop-in surface."""
+import copy
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+import dbx_distributed_pytorch_examples_b200 as b200
+from dbx_distributed_pytorch_examples_b200 import workloads
+
+pytestmark = pytest.mark.gpu
+
+
+def batch(step, n=32):
+    g = torch.Generator().manual_seed(1000 + step)
+    return torch.randn(n, 3, 32, 32, generator=g).cuda(), torch.randint(0, 10, (n,), generator=g).cuda()
+
+
+def make_pair():
+    torch.manual_seed(0)
+    ref = workloads.cifar_resnet18(10).cuda()
+    ours = copy.deepcopy(ref)
+    return ref, ours
+
+
+def test_drop_in_surface():
+    _, m = make_pair()
+    ddp = b200.B200DDP(m, device_ids=[0], output_device=0)
+    assert isinstance(ddp, torch.nn.parallel.DistributedDataParallel)
+    assert ddp.module is m
+    assert [p.data_ptr() for p in ddp.parameters()] == [p.data_ptr() for p in m.parameters()]
+    sizes = ddp.bucket_sizes_bytes()
+    assert sizes[0] >= 1024 * 1024 and all(s % 32 == 0 for s in sizes) and len(sizes) == 3
+    sd = ddp.module.state_dict()
+    assert all(v.untyped_storage().nbytes() < 16 * 1024 * 1024 for v in sd.values())  # copies, not heap views
+    with pytest.raises(ValueError):
+        b200.B200DDP(copy.deepcopy(m), device_ids=[0, 1])
+    with ddp.no_sync():
+        F.cross_entropy(ddp(batch(0)[0]), batch(0)[1]).backward()
+    assert all(p.grad is not None for p in m.parameters())
+
+
+def test_plain_mode_grads_and_user_optimizer_match_torch():
+    ref, m = make_pair()
+    ddp = b200.B200DDP(m, device_ids=[0])
+    o_ref = torch.optim.SGD(ref.parameters(), lr=1e-3, momentum=0.5)
+    o_our = torch.optim.SGD(ddp.parameters(), lr=1e-3, momentum=0.5)
+    for step in range(3):
+        x, y = batch(step)
+        o_ref.zero_grad(); o_our.zero_grad()
+        F.cross_entropy(ref(x), y).backward()
+        loss = F.cross_entropy(ddp(x), y); loss.backward()
+        for (n, a), b in zip(ref.named_parameters(), m.parameters()):
+            torch.testing.assert_close(b.grad, a.grad, rtol=1e-5, atol=1e-6, msg=lambda s: f"{n}: {s}")
+        o_ref.step(); o_our.step()
+    for a, b in zip(ref.parameters(), m.parameters()):
+        torch.testing.assert_close(b, a, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("opt", ["sgd", "adam", "adam_wd"])
+def test_fused_optimizer_matches_torch(opt):
+    ref, m = make_pair()
+    ddp = b200.B200DDP(m, device_ids=[0])
+    mk = {"sgd": lambda p: torch.optim.SGD(p, lr=1e-2, momentum=0.5),
+          "adam": lambda p: torch.optim.Adam(p, lr=1e-3),
+          "adam_wd": lambda p: torch.optim.Adam(p, lr=1e-3, weight_decay=1e-4)}[opt]
+    o_ref, o_our = mk(ref.parameters()), mk(ddp.parameters())
+    ddp.fuse_optimizer(o_our)
+    for step in range(4):
+        x, y = batch(step)
+        o_ref.zero_grad(); o_our.zero_grad()
+        l_ref = F.cross_entropy(ref(x), y); l_ref.backward(); o_ref.step()
+        l_our = F.cross_entropy(ddp(x), y); l_our.backward(); o_our.step()
+        torch.testing.assert_close(l_our, l_ref, rtol=1e-4, atol=1e-5)
+    tol = dict(rtol=1e-5, atol=1e-6) if opt == "sgd" else dict(rtol=1e-3, atol=2e-5)  # Adam's 1/sqrt(v) amplifies
+    for (n, a), b in zip(ref.named_parameters(), m.parameters()):
+        torch.testing.assert_close(b, a, msg=lambda s: f"{n}: {s}", **tol)
+    st = o_our.state[next(iter(m.parameters()))]
+    assert ("momentum_buffer" in st) if opt == "sgd" else (float(st["step"]) == 4 and "exp_avg_sq" in st)
+
+
+def test_bf16_model_with_syncbn_fusion_trains():
+    """bf16 channels_last ResNet-18 with fused SyncBN and fused SGD: loss follows an fp32 torch run."""
+    ref, m = make_pair()
+    m = b200.fuse_bn_relu(b200.convert_sync_batchnorm(m)).to(torch.bfloat16).to(memory_format=torch.channels_last)
+    ddp = b200.B200DDP(m, device_ids=[0])
+    o_ref = torch.optim.SGD(ref.parameters(), lr=1e-2, momentum=0.5)
+    o_our = ddp.fuse_optimizer(torch.optim.SGD(ddp.parameters(), lr=1e-2, momentum=0.5))
+    for step in range(10):
+        x, y = batch(step, 64)
+        o_ref.zero_grad(); o_our.zero_grad()
+        l_ref = F.cross_entropy(ref(x), y); l_ref.backward(); o_ref.step()
+        xb = x.bfloat16().contiguous(memory_format=torch.channels_last)
+        l_our = F.cross_entropy(ddp(xb).float(), y); l_our.backward(); o_our.step()
+        assert abs(float(l_our) - float(l_ref)) < 0.05 * float(l_ref) + 0.02, (step, float(l_our), float(l_ref))
+    torch.testing.assert_close(m.bn1.running_mean, ref.bn1.running_mean, rtol=5e-2, atol=2e-2)
+
+
+def test_comm_hook_compat():
+    _, m = make_pair()
+    ddp = b200.B200DDP(m, device_ids=[0])
+    seen = []
+
+    def hook(state, bucket):
+        seen.append((bucket.index(), bucket.is_last(), bucket.buffer().numel(), len(bucket.parameters())))
+        fut = torch.futures.Future()
+        fut.set_result(bucket.buffer())
+        return fut
+
+    ddp.register_comm_hook(None, hook)
+    x, y = batch(0)
+    F.cross_entropy(ddp(x), y).backward()
+    assert [s[0] for s in seen] == [0, 1, 2] and seen[-1][1] and sum(s[3] for s in seen) == 62

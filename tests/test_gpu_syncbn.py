@@ -1,0 +1,137 @@
+"""GPU, one rank: fused BN(+residual)+ReLU forward/backward through the C ABI against
+the numpy oracle and against torch's own F.batch_norm on the same device."""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+import dbx_distributed_pytorch_examples_b200 as b200
+from oracle import syncbn_ref
+
+pytestmark = pytest.mark.gpu
+
+TOL = {torch.float32: dict(rtol=1e-4, atol=1e-5), torch.bfloat16: dict(rtol=2e-2, atol=2e-2)}
+
+
+def rows(t):
+    C = t.shape[1]
+    return t.detach().float().permute(0, 2, 3, 1).reshape(-1, C).cpu().numpy()
+
+
+def run_ours(x, res, dy, w, b, rm, rv, relu, momentum=0.1, eps=1e-5):
+    bn = b200.B200SyncBatchNorm(x.shape[1], eps=eps, momentum=momentum, fuse_relu=relu).cuda()
+    with torch.no_grad():
+        bn.weight.copy_(w); bn.bias.copy_(b); bn.running_mean.copy_(rm); bn.running_var.copy_(rv)
+    x = x.clone().requires_grad_(True)
+    res = None if res is None else res.clone().requires_grad_(True)
+    y = bn(x, res)
+    y.backward(dy)
+    return bn, y, x.grad, None if res is None else res.grad
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("shape", [(8, 64, 16, 16), (4, 256, 7, 7), (3, 72, 5, 5), (130, 64, 32, 32), (2, 2048, 3, 3)])
+@pytest.mark.parametrize("mode", ["plain", "relu", "addrelu"])
+def test_against_oracle(dtype, shape, mode):
+    torch.manual_seed(sum(shape) + len(mode))
+    N, C, H, W = shape
+    relu, use_res = mode != "plain", mode == "addrelu"
+    mk = lambda s=1.0, o=0.0: (torch.randn(shape, device="cuda") * s + o).to(dtype).contiguous(memory_format=torch.channels_last)  # noqa: E731
+    x, res, dy = mk(2.0, 0.7), (mk() if use_res else None), mk()
+    w, b = torch.rand(C, device="cuda") + 0.5, torch.randn(C, device="cuda")
+    rm, rv = torch.randn(C, device="cuda") * 0.1, torch.rand(C, device="cuda") + 0.5
+    bn, y, dx, dres = run_ours(x, res, dy, w, b, rm, rv, relu)
+    ys, mean, invstd, _, rm_new, rv_new = syncbn_ref.forward(
+        [rows(x)], w.cpu().numpy(), b.cpu().numpy(), rm.cpu().numpy(), rv.cpu().numpy(), 1e-5, 0.1, relu,
+        [rows(res)] if use_res else None)
+    tol = TOL[dtype]
+    assert y.dtype == dtype and y.is_contiguous(memory_format=torch.channels_last)
+    np.testing.assert_allclose(rows(y), ys[0], **tol)
+    np.testing.assert_allclose(bn.running_mean.cpu().numpy(), rm_new, rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(bn.running_var.cpu().numpy(), rv_new, rtol=1e-4, atol=1e-6)
+    assert int(bn.num_batches_tracked) == 1
+    # the backward oracle takes the mask from OUR y (bf16 rounding can move values across 0)
+    dxs, drs, gws, gbs = syncbn_ref.backward([rows(dy)], [rows(x)], [rows(y)], w.cpu().numpy(), mean, invstd, relu)
+    scale = max(1.0, float(np.abs(dxs[0]).max()))
+    np.testing.assert_allclose(rows(dx), dxs[0], rtol=tol["rtol"], atol=tol["atol"] * scale)
+    gtol = dict(rtol=2e-3, atol=2e-3 * N * H * W ** 0.5) if dtype == torch.float32 else dict(rtol=3e-2, atol=0.5)
+    np.testing.assert_allclose(bn.weight.grad.cpu().numpy(), gws[0], **gtol)
+    np.testing.assert_allclose(bn.bias.grad.cpu().numpy(), gbs[0], **gtol)
+    if use_res:
+        np.testing.assert_allclose(rows(dres), drs[0], **tol)  # d_residual is the masked dy
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_against_torch_batch_norm(dtype):
+    torch.manual_seed(0)
+    shape = (32, 128, 14, 14)
+    x = torch.randn(shape, device="cuda").to(dtype).contiguous(memory_format=torch.channels_last)
+    dy = torch.randn(shape, device="cuda").to(dtype).contiguous(memory_format=torch.channels_last)
+    C = shape[1]
+    w, b = torch.rand(C, device="cuda") + 0.5, torch.randn(C, device="cuda")
+    rm, rv = torch.zeros(C, device="cuda"), torch.ones(C, device="cuda")
+    bn, y, dx, _ = run_ours(x, None, dy, w, b, rm, rv, True)
+    xr = x.clone().float().requires_grad_(True)
+    wr, br = w.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    rm2, rv2 = rm.clone(), rv.clone()
+    yr = torch.relu(F.batch_norm(xr, rm2, rv2, wr, br, True, 0.1, 1e-5))
+    yr.backward(dy.float())
+    tol = TOL[dtype]
+    torch.testing.assert_close(y.float(), yr, **tol)
+    torch.testing.assert_close(bn.running_mean, rm2, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(bn.running_var, rv2, rtol=1e-4, atol=1e-6)
+    if dtype == torch.float32:
+        torch.testing.assert_close(dx, xr.grad, rtol=1e-3, atol=1e-4)
+        torch.testing.assert_close(bn.weight.grad, wr.grad, rtol=1e-3, atol=1e-2)
+        torch.testing.assert_close(bn.bias.grad, br.grad, rtol=1e-3, atol=1e-2)
+
+
+def test_eval_mode_and_nchw_input_and_2d():
+    torch.manual_seed(1)
+    ref = torch.nn.BatchNorm2d(64).cuda()
+    with torch.no_grad():
+        ref.running_mean.normal_(); ref.running_var.uniform_(0.5, 2); ref.weight.uniform_(0.5, 1.5); ref.bias.normal_()
+    ours = b200.convert_sync_batchnorm(torch.nn.Sequential(ref))[0]
+    assert isinstance(ours, b200.B200SyncBatchNorm) and ours.weight is ref.weight
+    x = torch.randn(4, 64, 9, 9, device="cuda")  # NCHW-contiguous input is accepted
+    ours.eval(); ref.eval()
+    torch.testing.assert_close(ours(x), ref(x), rtol=1e-5, atol=1e-5)
+    ours.train(); ref.train()
+    y, yr = ours(x), ref(x)
+    torch.testing.assert_close(y, yr, rtol=1e-4, atol=1e-5)
+    # [N, C] input (BatchNorm1d shape)
+    bn1 = b200.B200SyncBatchNorm(32).cuda()
+    z = torch.randn(50, 32, device="cuda")
+    torch.testing.assert_close(bn1(z), F.batch_norm(z, None, None, bn1.weight, bn1.bias, True), rtol=1e-4, atol=1e-5)
+    with pytest.raises(ValueError, match="more than 1 value per channel"):
+        bn1(torch.randn(1, 32, device="cuda"))
+
+
+def test_momentum_none_and_no_running_stats():
+    x = torch.randn(16, 16, 4, 4, device="cuda")
+    ours = b200.B200SyncBatchNorm(16, momentum=None).cuda()
+    ref = torch.nn.BatchNorm2d(16, momentum=None).cuda()
+    for _ in range(3):
+        ours(x); ref(x)
+    torch.testing.assert_close(ours.running_mean, ref.running_mean, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(ours.running_var, ref.running_var, rtol=1e-4, atol=1e-6)
+    free = b200.B200SyncBatchNorm(16, track_running_stats=False, affine=False).cuda()
+    torch.testing.assert_close(free(x), F.batch_norm(x, None, None, None, None, True), rtol=1e-4, atol=1e-5)
+
+
+def test_linearity_and_large_layer_property():
+    """Size-independent checks on the largest BN layer of ResNet-50 224^2 at a reduced batch:
+    output statistics are (beta, gamma^2) and dx sums to zero per channel."""
+    torch.manual_seed(2)
+    x = (torch.randn(16, 64, 112, 112, device="cuda") * 3 + 1).bfloat16().contiguous(memory_format=torch.channels_last)
+    bn = b200.B200SyncBatchNorm(64).cuda()
+    with torch.no_grad():
+        bn.weight.fill_(2.0); bn.bias.fill_(0.5)
+    xr = x.clone().requires_grad_(True)
+    y = bn(xr)
+    m = y.float().mean((0, 2, 3)); v = y.float().var((0, 2, 3), unbiased=False)
+    torch.testing.assert_close(m, torch.full_like(m, 0.5), rtol=0, atol=2e-2)
+    torch.testing.assert_close(v, torch.full_like(v, 4.0), rtol=2e-2, atol=0)
+    y.backward(torch.randn_like(y))
+    s = xr.grad.float().sum((0, 2, 3))
+    assert float(s.abs().max()) < 0.05 * float(xr.grad.float().abs().sum((0, 2, 3)).max())

@@ -1,0 +1,153 @@
+"""CPU: host-side logic of the drop-ins, and the C-ABI library's export table.
+No compute entry point is called here (there is no GPU in the build container)."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+import torch.nn as nn
+
+import dbx_distributed_pytorch_examples_b200 as b200
+from dbx_distributed_pytorch_examples_b200 import _lib, ddp, fusion, workloads
+from oracle import ddp_ref
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    header = open(os.path.join(ROOT, "include", "b200dp.h")).read()
+    declared = set(re.findall(r"\b(b200dp_[a-z0-9_]+)\s*\(", header))
+    assert declared, "no declarations found"
+    handle = ctypes.CDLL(_lib.LIB_PATH)
+    for name in sorted(declared):
+        assert hasattr(handle, name), f"{name} is declared in include/b200dp.h but not exported"
+    assert declared == set(_lib.exported_symbols())
+    lib = _lib.lib()
+    assert lib.b200dp_version() == 100
+    assert b"invalid" in lib.b200dp_error_string(-1)
+    assert lib.b200dp_bn_scratch_bytes(64) > 0
+
+
+def test_argument_checks_need_no_gpu():
+    lib = _lib.lib()
+    # contract violations are rejected before any CUDA call
+    assert lib.b200dp_augment_u8_bf16(None, -1, 8, 8, None, 0, 8, 8, None, None, None, None) == -1
+    assert lib.b200dp_bn_fwd_stats(None, 7, 4, 64, None, None, None, 0, None) == -2
+    assert lib.b200dp_bn_fwd_stats(None, _lib.BF16, 4, 60, None, None, None, 0, None) == -2  # C % 8
+    assert lib.b200dp_bucket_pack(None, None, None, 2000, None, 0, 1.0, None) == -5
+
+
+def test_draws_match_torchvision_golden(golden):
+    for name, src in (("transform_cifar.npz", 32), ("transform_crop56.npz", 64)):
+        g = golden(name)
+        torch.manual_seed(int(g["seed"]))
+        got = b200.draw_crop_flip_params(len(g["params"]), (src, src), (int(g["out_hw"]),) * 2, int(g["pad"]))
+        assert np.array_equal(got.numpy(), g["params"])  # bit-exact indices
+
+
+def test_draws_match_live_torchvision():
+    from torchvision import transforms as T
+    torch.manual_seed(99)
+    want = []
+    for _ in range(40):
+        i, j, _, _ = T.RandomCrop.get_params(torch.zeros(3, 40, 40), (32, 32))
+        want.append((i, j, int(torch.rand(1) < 0.5)))
+    gen = torch.Generator().manual_seed(99)
+    got = b200.draw_crop_flip_params(40, (32, 32), (32, 32), 4, generator=gen)
+    assert got.tolist() == [list(w) for w in want]
+    # equal sizes: get_params draws nothing, only the flip consumes the generator
+    gen = torch.Generator().manual_seed(5)
+    ref = torch.Generator().manual_seed(5)
+    got = b200.draw_crop_flip_params(10, (32, 32), (32, 32), 0, generator=gen)
+    assert got[:, :2].abs().sum() == 0
+    assert got[:, 2].tolist() == [int(torch.rand(1, generator=ref) < 0.5) for _ in range(10)]
+    with pytest.raises(ValueError):
+        b200.draw_crop_flip_params(1, (8, 8), (16, 16))
+
+
+def test_bucket_plan_matches_ddp_assignment():
+    model = workloads.cifar_resnet18()
+    params = list(reversed(list(model.parameters())))
+    numels = [p.numel() for p in params]
+    for world in (1, 2, 8):
+        offsets, buckets, total = ddp.plan_buckets(numels, 4, world, 25 * 1024 * 1024)
+        assert all(o % 8 == 0 for o in offsets)
+        assert all(n % (8 * world) == 0 for _, n, _, _ in buckets)
+        # contiguous, non-overlapping, every parameter inside its bucket
+        assert buckets[0][0] == 0 and sum(n for _, n, _, _ in buckets) == total
+        for (s, n, p0, p1) in buckets:
+            assert offsets[p0] == s and offsets[p1 - 1] + numels[p1 - 1] <= s + n
+    # same grouping as torch's _compute_bucket_assignment_by_size up to the 8-element padding
+    want = ddp_ref.bucket_assignment([4 * n for n in numels])
+    _, buckets, _ = ddp.plan_buckets(numels, 4, 1, 25 * 1024 * 1024)
+    assert [list(range(p0, p1)) for _, _, p0, p1 in buckets] == want
+
+
+def test_convert_and_fuse_keep_state_dict_layout():
+    model = workloads.cifar_resnet18()
+    keys = list(model.state_dict().keys())
+    w = model.layer1[0].bn1.weight
+    out = b200.convert_sync_batchnorm(model)
+    assert list(out.state_dict().keys()) == keys
+    assert out.layer1[0].bn1.weight is w  # Parameters are shared, not copied
+    n_bn = sum(isinstance(m, b200.B200SyncBatchNorm) for m in out.modules())
+    assert n_bn == 20  # setup/resnet18.py has 20 BatchNorm2d layers
+    assert not any(isinstance(m, nn.BatchNorm2d) for m in out.modules())
+    b200.fuse_bn_relu(out)
+    assert list(out.state_dict().keys()) == keys
+    assert out.bn1.fuse_relu and isinstance(out.relu, nn.Identity)
+    assert out.layer2[0].bn1.fuse_relu and out.layer2[0].bn2.fuse_relu
+    assert not out.layer2[0].skip_connection[1].fuse_relu  # projection BN has no activation
+    # statistics and affine parameters stay fp32 through a bf16 cast
+    out.to(torch.bfloat16)
+    assert out.bn1.weight.dtype == torch.float32 and out.bn1.running_var.dtype == torch.float32
+    assert out.conv1.weight.dtype == torch.bfloat16
+
+
+def test_torchvision_resnet50_is_recognised():
+    model = b200.fuse_bn_relu(b200.convert_sync_batchnorm(workloads.resnet50(10)))
+    bns = [m for m in model.modules() if isinstance(m, b200.B200SyncBatchNorm)]
+    assert len(bns) == 53
+    assert sum(m.fuse_relu for m in bns) == 53 - 4  # all but the 4 downsample BNs
+    assert model.layer1[0].forward.__func__ is fusion._bottleneck_forward
+
+
+def test_no_cpu_fallback():
+    bn = b200.B200SyncBatchNorm(8)
+    with pytest.raises(ValueError, match="expected input tensor to be on GPU"):
+        bn(torch.randn(2, 8, 4, 4))
+    with pytest.raises(ValueError, match="no CPU path"):
+        b200.B200DDP(nn.Linear(4, 4))
+    frozen = nn.Linear(4, 4).requires_grad_(False)
+    with pytest.raises(RuntimeError, match="doesn't have any parameter that requires a gradient"):
+        b200.B200DDP(frozen)
+    if not torch.cuda.is_available():
+        with pytest.raises(Exception):
+            b200.BatchTransform(8)(torch.zeros(2, 8, 8, 3, dtype=torch.uint8))
+
+
+def test_missing_library_fails_loudly(monkeypatch):
+    monkeypatch.setattr(_lib, "_lib", None)
+    monkeypatch.setattr(_lib, "LIB_PATH", "/nonexistent/libb200dp.so")
+    with pytest.raises(_lib.B200DPError, match="no CPU or eager fallback"):
+        _lib.lib()
+
+
+def test_workload_matches_reference_model():
+    ref_path = "/root/reference/setup/resnet18.py"
+    if not os.path.exists(ref_path):
+        pytest.skip("reference tree not mounted (GPU box)")
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("_ref_resnet18", ref_path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    torch.manual_seed(0)
+    ours = workloads.cifar_resnet18(10)
+    torch.manual_seed(0)
+    ref = mod.ResNet18(10)
+    sa, sb = ours.state_dict(), ref.state_dict()
+    assert list(sa) == list(sb) and all(torch.equal(sa[k], sb[k]) for k in sa)
+    x = torch.randn(4, 3, 32, 32)
+    assert torch.equal(ours(x), ref(x))
