@@ -1,0 +1,358 @@
+#!/usr/bin/env python
+"""Headline benchmark: ResNet-50 224^2 bf16 channels_last, SyncBN + DDP + GPU input transform.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+One "step" = one pass of the data-parallel hot path over one batch of 256 synthetic images per
+GPU (BASELINE.json config 4): uint8 256x256 source images -> crop 224 / flip / normalize kernel
+-> torchvision ResNet-50 (convolutions on cuDNN) with fused SyncBN(+add)+ReLU kernels ->
+cross-entropy -> backward with the gradient buckets packed, all-reduced over NVLink peer
+memory, averaged and applied by the fused SGD-momentum kernel.
+
+`value`   images/s, whole job, source images already resident in HBM, CUDA-event timed.
+`e2e`     same metric through the public API with the source images in pinned HOST memory
+          (H2D copy inside the timed region) and loss.item() read back every step.
+`roofline` the library kernel with the largest share of the step, timed per launch with CUDA
+          events in a separate instrumented pass of the same step.
+`cpu_baseline` / `--impl reference`: the reference's own software stack on the host cores —
+          torchvision's per-sample CPU transform pipeline + stock DistributedDataParallel over
+          gloo + torch.optim.SGD on a torchvision ResNet-50 (fp32, reduced batch, stated).
+"""
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+import torch.nn.functional as F  # noqa: E402
+
+METRIC = "resnet50_224_bf16_ddp_images_per_sec"
+UNIT = "images/s"
+PER_GPU_BATCH = 256
+SRC_HW, OUT_HW, CLASSES = 256, 224, 1000
+
+
+# ------------------------------------------------------------------ reference / CPU arm
+def cpu_reference(steps, warmup, batch=16, threads=None):
+    """The reference's stack on host cores: per-sample torchvision transforms
+    (02_deepspeed/03_1k_imagenet_deepspeed_resnet.py:45-53 minus the resize), stock DDP over
+    gloo (01_torch_distributor/01_basic_torch_distributor.py:269,291 with backend gloo),
+    SGD(lr=1e-3, momentum=0.5) (:294), torchvision ResNet-50 fp32."""
+    import torchvision
+    from PIL import Image
+    from torch.nn.parallel import DistributedDataParallel as DDP
+    from torchvision import transforms as T
+
+    threads = threads or os.cpu_count()
+    torch.set_num_threads(threads)
+    own_group = not dist.is_initialized()
+    if own_group:
+        store = dist.TCPStore("127.0.0.1", 0, 1, True)
+        dist.init_process_group("gloo", store=store, rank=0, world_size=1)
+    torch.manual_seed(0)
+    model = DDP(torchvision.models.resnet50(weights=None, num_classes=CLASSES))
+    opt = torch.optim.SGD(model.parameters(), lr=1e-3, momentum=0.5)
+    pipeline = T.Compose([T.RandomCrop(OUT_HW), T.RandomHorizontalFlip(), T.ToTensor(),
+                          T.Normalize([0.485, 0.456, 0.406], [0.229, 0.224, 0.225])])
+    g = torch.Generator().manual_seed(1)
+    src = torch.randint(0, 256, (batch, SRC_HW, SRC_HW, 3), dtype=torch.uint8, generator=g).numpy()
+    images = [Image.fromarray(a) for a in src]
+    target = torch.randint(0, CLASSES, (batch,), generator=g)
+    model.train()
+
+    def step():
+        x = torch.stack([pipeline(im) for im in images])
+        opt.zero_grad()
+        loss = F.cross_entropy(model(x), target)
+        loss.backward()
+        opt.step()
+        return loss.item()
+
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    dt = time.perf_counter() - t0
+    if own_group:
+        dist.destroy_process_group()
+    return {"value": batch * steps / dt, "ms_per_step": 1e3 * dt / steps, "cores": threads, "batch": batch,
+            "steps": steps}
+
+
+def run_reference_arm(args, rank):
+    if rank != 0:
+        return
+    steps, warmup = max(1, min(args.steps, 4)), max(1, min(args.warmup, 1))
+    r = cpu_reference(steps, warmup, batch=16)
+    sample = (f"stock torch DDP(gloo, world 1)+torchvision CPU transforms+SGD, ResNet-50 fp32, batch {r['batch']}, "
+              f"{steps} timed steps after {warmup} warm-up (requested {args.steps}/{args.warmup}, bounded for CPU time)")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": steps, "warmup": warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "resnet50_224_syncbn_ddp_augment", "per_gpu_batch": r["batch"], "image": OUT_HW,
+                   "parallelism": "cpu-gloo-1"},
+        "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "reference", "sample": sample},
+        "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------ clocks
+class ClockSampler:
+    """Samples SM clock and throttle reasons with NVML while the timed region runs."""
+
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz, self._stop = [], set(), None, threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[index]) if vis and vis.split(",")[index].isdigit() else index
+            self.nv, self.h = pynvml, pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:  # NVML missing: report nulls rather than fail the bench
+            self.nv = None
+        self.thread = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                mask = self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                self.reasons.update(name for bit, name in self.REASONS.items() if mask & bit)
+            except Exception:
+                pass
+            self._stop.wait(0.1)
+
+    def __enter__(self):
+        if self.nv:
+            self.thread.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        if self.nv:
+            self.thread.join()
+
+    def summary(self):
+        return {"sm_mhz": statistics.median(self.samples) if self.samples else None,
+                "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+# ------------------------------------------------------------------ per-kernel pass
+def algorithmic_bytes(name, a):
+    """Bytes each entry point must move at minimum, from its arguments."""
+    es = lambda code: 2 if code == 1 else 4  # noqa: E731
+    if name == "b200dp_bn_fwd_stats":
+        return a[2] * a[3] * es(a[1])
+    if name == "b200dp_bn_fwd_apply":
+        return a[4] * a[5] * es(a[3]) * (2 + (1 if a[1] else 0))
+    if name == "b200dp_bn_bwd_reduce":
+        return a[4] * a[5] * es(a[3]) * (2 + (1 if a[10] == 2 else 0))
+    if name == "b200dp_bn_bwd_apply":
+        return a[6] * a[7] * es(a[5]) * (3 + (1 if a[14] == 2 else 0) + (1 if a[4] else 0))
+    if name == "b200dp_augment_u8_bf16":
+        return a[1] * a[6] * a[7] * 3 * 3
+    if name == "b200dp_allreduce_update":  # world 1: g + master r/w + momentum r/w + param copy
+        e = es(a[2])
+        return a[6] * (e + 8 + 8 + (e if a[7] else 0))
+    return 0
+
+
+class KernelProfiler:
+    def __init__(self):
+        self.records = []
+
+    def __call__(self, name, fn, args):
+        # every caller launches on torch's current stream (syncbn/transform: the ambient one,
+        # ddp: inside `with torch.cuda.stream(comm_stream)`); record on exactly that stream
+        s = torch.cuda.current_stream()
+        assert s.cuda_stream == int(args[-1] or 0), "kernel was not launched on the current stream"
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(s)
+        rc = fn(*args)
+        e1.record(s)
+        self.records.append((name, algorithmic_bytes(name, args), e0, e1))
+        return rc
+
+    def table(self):
+        torch.cuda.synchronize()
+        out = {}
+        for name, nbytes, e0, e1 in self.records:
+            t = out.setdefault(name, {"launches": 0, "ms": 0.0, "bytes": 0})
+            t["launches"] += 1
+            t["ms"] += e0.elapsed_time(e1)
+            t["bytes"] += nbytes
+        return out
+
+
+# ------------------------------------------------------------------ our arm
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=PER_GPU_BATCH, help="per-GPU batch (256 is the named config)")
+    ap.add_argument("--optimizer", default="sgd", choices=["sgd", "adam"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-kernel-pass", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference_arm(args, rank)
+        return
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run for N > 1")
+    if args.warmup < 3:
+        raise SystemExit("at least 3 warm-up steps are required by the timing rules")
+
+    import dbx_distributed_pytorch_examples_b200 as b200
+    from dbx_distributed_pytorch_examples_b200 import _lib, workloads
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    torch.backends.cudnn.benchmark = True
+
+    torch.manual_seed(0)
+    model = workloads.resnet50(CLASSES)
+    model = b200.fuse_bn_relu(b200.convert_sync_batchnorm(model)).to(dev)
+    model = model.to(torch.bfloat16).to(memory_format=torch.channels_last)
+    ddp = b200.B200DDP(model, device_ids=[local_rank], output_device=local_rank)
+    if args.optimizer == "sgd":  # 01_basic_torch_distributor.py:294
+        opt = torch.optim.SGD(ddp.parameters(), lr=1e-3, momentum=0.5)
+    else:                        # 02_cifar_torch_distributor_resnet.py:213
+        opt = torch.optim.Adam(ddp.parameters(), lr=1e-3)
+    ddp.fuse_optimizer(opt)
+    tf = b200.BatchTransform(OUT_HW, device=dev)
+
+    B = args.batch
+    host_u8 = workloads.synthetic_u8_images(B, SRC_HW, seed=100 + rank, pin=True)
+    host_y = torch.randint(0, CLASSES, (B,), generator=torch.Generator().manual_seed(100 + rank)).pin_memory()
+    dev_u8, dev_y = host_u8.to(dev), host_y.to(dev)
+    gen = torch.Generator().manual_seed(1234 + rank)
+    ddp.train()
+
+    def step(images, labels):
+        x = tf(images, generator=gen)
+        y = labels if labels.is_cuda else labels.to(dev, non_blocking=True)
+        opt.zero_grad()
+        loss = F.cross_entropy(ddp(x).float(), y)
+        loss.backward()
+        opt.step()
+        return loss
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, n):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms)
+
+    for _ in range(args.warmup):
+        step(dev_u8, dev_y)
+    _lib.CALLS.clear()
+    with ClockSampler(local_rank) as clocks:
+        ms_dev = timed(lambda: step(dev_u8, dev_y), args.steps)
+    launches = sum(_lib.CALLS.values())
+    loss_dev = float(step(dev_u8, dev_y).detach())
+
+    for _ in range(2):
+        step(host_u8, host_y).item()
+    ms_e2e = timed(lambda: step(host_u8, host_y).item(), args.steps)
+    ddp.comm.check_error()
+
+    images = B * world * args.steps
+    value = images / (ms_dev / 1e3)
+    e2e = images / (ms_e2e / 1e3)
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": "resnet50_224_syncbn_ddp_augment", "global_batch": B * world, "per_gpu_batch": B,
+                   "source_image": SRC_HW, "image": OUT_HW, "classes": CLASSES, "optimizer": args.optimizer,
+                   "parallelism": f"dp{world}", "l2": "inputs_exceed_l2 (>=10 GB of activations per step)"},
+        "e2e": {"value": e2e, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
+                "h2d_bytes_per_step": host_u8.numel() + host_y.numel() * 8 + B * 12, "d2h_bytes_per_step": 4},
+        "gpu_launches": launches,
+        "clocks": clocks.summary(),
+        "loss": loss_dev,
+    }
+
+    if rank == 0 and not args.no_kernel_pass:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = peaks.get("hbm_gbs", 6650.0)
+        line["roofline_peak_source"] = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+    if not args.no_kernel_pass:
+        # every rank runs the instrumented steps (they contain collectives); rank 0 reports
+        prof = KernelProfiler()
+        _lib.PROFILER = prof
+        for _ in range(2):
+            step(dev_u8, dev_y)
+        _lib.PROFILER = None
+        table = prof.table()
+        if rank == 0:
+            top = max((k for k in table if table[k]["bytes"] > 0), key=lambda k: table[k]["ms"])
+            t = table[top]
+            achieved = t["bytes"] / (t["ms"] / 1e3) / 1e9
+            step_ms = ms_dev / args.steps
+            line["roofline"] = {"kernel": top, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                                "frac": achieved / peak, "traffic": None,
+                                "launches_per_step": t["launches"] // 2, "ms_per_step": t["ms"] / 2,
+                                "share_of_step": t["ms"] / 2 / step_ms}
+            line["kernels"] = {k: {"launches_per_step": v["launches"] // 2, "ms_per_step": round(v["ms"] / 2, 4),
+                                   "gbps": round(v["bytes"] / (v["ms"] / 1e3) / 1e9, 1) if v["ms"] > 0 else None}
+                               for k, v in sorted(table.items())}
+
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        r = cpu_reference(steps=3, warmup=1, batch=16)
+        line["cpu_baseline"] = {
+            "value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "reference",
+            "sample": "stock torch DDP(gloo, world 1)+torchvision CPU transforms+SGD, ResNet-50 224^2 fp32, "
+                      "batch 16, 3 timed steps after 1 warm-up"}
+    if world > 1:
+        dist.barrier()
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

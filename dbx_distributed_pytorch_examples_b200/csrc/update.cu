@@ -289,6 +289,7 @@ extern "C" int b200dp_allreduce_update(b200dp_comm* comm, size_t grad_heap_off, 
   if ((grad_dtype != B200DP_F32 && grad_dtype != B200DP_BF16) ||
       (param_dtype != B200DP_F32 && param_dtype != B200DP_BF16))
     return B200DP_EUNSUPPORTED;
+  if (grad_dtype != param_dtype) return B200DP_EUNSUPPORTED;  // one element type per arena
   if ((grad_heap_off & 15) || (param_heap_off & 15)) return B200DP_EALIGN;
   const size_t gsz = grad_dtype == B200DP_BF16 ? 2 : 4, psz = param_dtype == B200DP_BF16 ? 2 : 4;
   if (grad_heap_off + (size_t)(elem_offset + numel) * gsz > comm->heap_bytes) return B200DP_EINVAL;

@@ -205,10 +205,12 @@ class B200DDP(DistributedDataParallel):
                 a.flat_grad = self.comm.heap_view(a.grad_off, a.total, a.dtype)
                 a.flat_param = self.comm.heap_view(a.param_off, a.total, a.dtype)
                 for p, off in zip(a.params, a.offsets):
-                    view = a.flat_param[off:off + p.numel()].view(p.shape)
+                    # keep the parameter's physical layout (channels_last conv weights stay
+                    # KRSC): gradients then arrive in the same layout and pack as flat memory
+                    view = _strided_like(a.flat_param[off:off + p.numel()], p)
                     view.copy_(p.data)
                     p.data = view
-                    a.grad_views.append(a.flat_grad[off:off + p.numel()].view(p.shape))
+                    a.grad_views.append(_strided_like(a.flat_grad[off:off + p.numel()], p))
                 for (start, numel, p0, p1) in a.buckets:
                     b = _BucketState(a, len(self._buckets), start, numel, p0, p1)
                     self._buckets.append(b)
@@ -313,8 +315,8 @@ class B200DDP(DistributedDataParallel):
                 if g is None:
                     a.grad_views[k].zero_()
                     continue
-                if g.dtype != a.dtype or not g.is_contiguous():
-                    g = g.to(a.dtype).contiguous()
+                if g.dtype != a.dtype or (g.stride() != p.stride() and p.numel() > 1):
+                    g = torch.empty_like(p).copy_(g)  # rare: layout or dtype differs from the parameter's
                 g.record_stream(self._comm_stream)
                 b.srcs[n] = g.data_ptr()
                 b.numels[n] = p.numel()
@@ -458,6 +460,14 @@ class B200DDP(DistributedDataParallel):
 
     def _get_ddp_logging_data(self):
         return {"backend_name": "b200dp-nvlink-p2p", "world_size": self.world, "rank": self.rank}
+
+
+def _strided_like(flat: torch.Tensor, p: torch.Tensor) -> torch.Tensor:
+    """View of the 1-D slice `flat` with p's shape and, when p is a dense permutation
+    (e.g. channels_last conv weights), p's strides."""
+    if p.is_contiguous() or torch.empty_like(p).stride() != p.stride():
+        return flat.view(p.shape)
+    return flat.as_strided(p.shape, p.stride())
 
 
 def _clone_state_dict_hook(module, state_dict, prefix, local_metadata):
