@@ -73,7 +73,7 @@ _lib = None
 # stream the call was given (bench.py's per-kernel roofline pass).
 CALLS = {}
 PROFILER = None
-_COMPUTE = ("b200dp_augment_u8_bf16", "b200dp_bn_fwd_stats", "b200dp_bn_fwd_apply", "b200dp_bn_inference",
+_COMPUTE = ("b200dp_augment_u8_bf16", "b200dp_bn_fwd_stats", "b200dp_bn_fwd_stats_noalloc", "b200dp_bn_fwd_apply", "b200dp_bn_inference",
             "b200dp_bn_bwd_reduce", "b200dp_bn_bwd_apply", "b200dp_bucket_pack", "b200dp_allreduce_update",
             "b200dp_comm_barrier")
 
@@ -109,6 +109,7 @@ _SIGNATURES = {
                                        POINTER(c_float), POINTER(c_float), _VP, _VP]),
     "b200dp_bn_scratch_bytes": (c_size_t, [c_int]),
     "b200dp_bn_fwd_stats": (c_int, [_VP, c_int, c_int64, c_int, _VP, _VP, _VP, c_uint32, _VP]),
+    "b200dp_bn_fwd_stats_noalloc": (c_int, [_VP, c_int, c_int64, c_int, _VP, _VP]),
     "b200dp_bn_fwd_apply": (c_int, [_VP, _VP, _VP, c_int, c_int64, c_int, _VP, _VP, _VP, c_float,
                                     c_float, _VP, _VP, _VP, _VP, _VP, c_int, _VP, c_uint32, _VP]),
     "b200dp_bn_inference": (c_int, [_VP, _VP, _VP, c_int, c_int64, c_int, _VP, _VP, _VP, _VP,

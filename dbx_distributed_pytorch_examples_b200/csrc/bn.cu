@@ -20,6 +20,8 @@
 // Algorithmic traffic per element (bf16): stats 2 B; fwd apply 4 B (+2 with a
 // residual); bwd reduce 4 B; bwd apply 6 B (+2 for d_residual); the ReLU mask
 // is recomputed from x (mode 1) or read from y (mode 2, +2 B per bwd pass).
+#include <mutex>
+
 #include "common.cuh"
 
 namespace {
@@ -637,6 +639,71 @@ extern "C" int b200dp_bn_fwd_stats(const void* x, int dtype, int64_t M, int C, v
     const Grid2 g = plan_grid<float>(M, C, kOccFwd);
     bn_stats_kernel<float><<<dim3(g.gx, g.gy), kT, 0, s>>>(static_cast<const float*>(x), M, C,
                                                            scratch, stats_local, P, seq);
+  }
+  B200DP_LAUNCH_CHECK();
+  return B200DP_OK;
+}
+
+// ---- statistics without any allocation ---------------------------------------
+// Some hosts may not let a library allocate device memory: a serving process or
+// another framework's arena that has handed out every byte of HBM to its own pool
+// and passes us nothing but the input and output buffers, or a launch path that must
+// never block (cudaMalloc takes a device-wide lock and can synchronise the GPU).
+// For them the reduction scratch of the statistics kernel lives in this fixed
+// array, part of the library image: every GPU that loads libb200dp.so holds these
+// kBnStaticScratchBytes bytes until the process exits.
+namespace {
+constexpr size_t kBnStaticScratchBytes = kScratchBytes;  // 307,712 bytes
+static __device__ __align__(256) unsigned char g_bn_static_scratch[kBnStaticScratchBytes];
+
+constexpr int kMaxDevices = 64;
+void* g_bn_static_scratch_addr[kMaxDevices];  // device address of the array, per device ordinal
+std::mutex g_bn_static_mutex;
+
+// In host code `g_bn_static_scratch` is only a handle for the symbol, not an address a
+// kernel may dereference: ask the runtime for the device address, once per device, with
+// that device current.
+int bn_static_scratch(void** out) {
+  int dev = -1;
+  B200DP_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return B200DP_EUNSUPPORTED;
+  std::lock_guard<std::mutex> lock(g_bn_static_mutex);
+  if (!g_bn_static_scratch_addr[dev]) {
+    void* p = nullptr;
+    B200DP_CUDA_TRY(cudaGetSymbolAddress(&p, g_bn_static_scratch));
+    if (!p) return B200DP_ESTATE;
+    g_bn_static_scratch_addr[dev] = p;
+  }
+  *out = g_bn_static_scratch_addr[dev];
+  return B200DP_OK;
+}
+}  // namespace
+
+extern "C" int b200dp_bn_fwd_stats_noalloc(const void* x, int dtype, int64_t M, int C,
+                                           float* stats_local, b200dp_stream_t stream) {
+  if (C > B200DP_BN_NOALLOC_MAX_CHANNELS) return B200DP_ETOOBIG;  // the fixed scratch is sized for this
+  int rc = check_common(x, nullptr, nullptr, dtype, M, C);
+  if (rc) return rc;
+  if (!stats_local) return B200DP_EINVAL;
+  void* scratch = nullptr;
+  if ((rc = bn_static_scratch(&scratch))) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  // The array is shared by every call and keeps what the last one left in it.  Only the
+  // "last CTA" tickets have to start at zero; partials and counts are written before they
+  // are read.  Clearing them here also recovers from a call that was cut short.
+  B200DP_CUDA_TRY(cudaMemsetAsync((char*)scratch + kScratchTickets, 0, kScratchCounts - kScratchTickets, s));
+  const b200dp_peers P = b200dp_make_peers(nullptr);
+  Grid2 g;
+  if (dtype == B200DP_BF16) {
+    g = plan_grid<__nv_bfloat16>(M, C, kOccFwd);
+    if ((size_t)g.gx * g.gy * kCV * Vec<__nv_bfloat16>::N > (size_t)kMaxPartials) return B200DP_ETOOBIG;
+    bn_stats_kernel<__nv_bfloat16><<<dim3(g.gx, g.gy), kT, 0, s>>>(
+        static_cast<const __nv_bfloat16*>(x), M, C, scratch, stats_local, P, 0);
+  } else {
+    g = plan_grid<float>(M, C, kOccFwd);
+    if ((size_t)g.gx * g.gy * kCV * Vec<float>::N > (size_t)kMaxPartials) return B200DP_ETOOBIG;
+    bn_stats_kernel<float><<<dim3(g.gx, g.gy), kT, 0, s>>>(static_cast<const float*>(x), M, C,
+                                                           scratch, stats_local, P, 0);
   }
   B200DP_LAUNCH_CHECK();
   return B200DP_OK;

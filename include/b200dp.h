@@ -116,6 +116,28 @@ int b200dp_bn_fwd_stats(const void* x, int dtype, int64_t M, int C,
                         void* scratch, float* stats_local, b200dp_comm* comm,
                         uint32_t seq, b200dp_stream_t stream);
 
+/* b200dp_bn_fwd_stats for callers that must not allocate device memory.
+ * No counterpart in the reference: this is an addition of this library for hosts
+ * that give a library no way to allocate — a serving process or another
+ * framework's arena that owns all of HBM through its own pool and hands over only
+ * the input and output buffers, or a launch path that may never block on the
+ * allocator's device-wide lock.  The reduction scratch is a fixed array inside the
+ * library image (307,712 bytes, held by every GPU that loads the library until
+ * the process exits); the call performs no cudaMalloc / cudaFree and uses no
+ * allocating library routine.  Single-GPU statistics only (no communicator).
+ *   - C larger than B200DP_BN_NOALLOC_MAX_CHANNELS returns B200DP_ETOOBIG.
+ *   - The first call on a device looks up the array's device address
+ *     (cudaGetSymbolAddress) with that device current; make that first call
+ *     outside any stream capture.
+ *   - All calls on a device share the one array, which keeps the previous call's
+ *     contents: the entry point clears the part that must start at zero on the
+ *     given stream before the kernel.  Calls that overlap on the GPU (different
+ *     streams without ordering between them) race on it — serialise them.
+ * Output as b200dp_bn_fwd_stats: stats_local fp32 [2*C+1] = mean, M2, count. */
+#define B200DP_BN_NOALLOC_MAX_CHANNELS 4096
+int b200dp_bn_fwd_stats_noalloc(const void* x, int dtype, int64_t M, int C,
+                                float* stats_local, b200dp_stream_t stream);
+
 /* Merge the ranks' statistics by count (batch_norm_gather_stats_with_counts),
  * then y = act((x-mean)*invstd*weight + bias [+ residual]), act = ReLU when
  * `relu` != 0 (batch_norm_elemt + the epilogues of setup/resnet18.py:23-26).
