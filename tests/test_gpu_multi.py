@@ -1,0 +1,226 @@
+"""GPU, 2 ranks (one process per GPU, NCCL only for set-up and as the comparison baseline):
+SyncBN statistics exchange, the fused all-reduce + optimizer kernel over peer memory, and the
+BASELINE config-1 training run (reference ResNet-18, batch 128/rank, SGD 1e-3/0.5, 200 steps)
+against the golden loss curve of stock DDP.  Run with `gpurun --gpus 2`."""
+import os
+
+import numpy as np
+import pytest
+
+from dbx_distributed_pytorch_examples_b200 import TorchDistributor
+
+pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def _init():
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", rank))
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.deterministic = True
+    return rank, dist.get_world_size()
+
+
+def _w_syncbn():
+    import torch
+    import torch.distributed as dist
+    import dbx_distributed_pytorch_examples_b200 as b200
+    rank, world = _init()
+    g = np.load(os.path.join(GOLD, "syncbn.npz"))
+    C, eps, mom = 16, float(g["eps"]), float(g["momentum"])
+
+    def nchw(rows):  # fixture rows are [N*4*4, C]
+        t = torch.from_numpy(rows).cuda().view(-1, 4, 4, C).permute(0, 3, 1, 2)
+        return t.contiguous(memory_format=torch.channels_last)
+
+    def rows(t):
+        return t.detach().float().permute(0, 2, 3, 1).reshape(-1, C).cpu().numpy()
+
+    for tag, relu, res in [("plain", False, False), ("relu", True, False), ("addrelu", True, True)]:
+        bn = b200.B200SyncBatchNorm(C, eps=eps, momentum=mom, fuse_relu=relu).cuda()
+        with torch.no_grad():
+            bn.weight.copy_(torch.from_numpy(g[f"{tag}_w"])); bn.bias.copy_(torch.from_numpy(g[f"{tag}_b"]))
+            bn.running_mean.copy_(torch.from_numpy(g[f"{tag}_rm"])); bn.running_var.copy_(torch.from_numpy(g[f"{tag}_rv"]))
+        x = nchw(g[f"{tag}_x{rank}"]).requires_grad_(True)
+        r = nchw(g[f"{tag}_r{rank}"]).requires_grad_(True) if res else None
+        y = bn(x, r)
+        y.backward(nchw(g[f"{tag}_dy{rank}"]))
+        np.testing.assert_allclose(rows(y), g[f"{tag}_y{rank}"], rtol=1e-4, atol=1e-5)
+        np.testing.assert_allclose(rows(x.grad), g[f"{tag}_dx{rank}"], rtol=1e-3, atol=1e-5)
+        np.testing.assert_allclose(bn.running_mean.cpu().numpy(), g[f"{tag}_rm_new"], rtol=1e-5, atol=1e-6)
+        np.testing.assert_allclose(bn.running_var.cpu().numpy(), g[f"{tag}_rv_new"], rtol=1e-4, atol=1e-6)
+        gw, gb = bn.weight.grad.clone(), bn.bias.grad.clone()  # rank-local; their sum is autograd's total
+        dist.all_reduce(gw); dist.all_reduce(gb)
+        np.testing.assert_allclose(gw.cpu().numpy(), g[f"{tag}_dw"], rtol=1e-3, atol=1e-4)
+        np.testing.assert_allclose(gb.cpu().numpy(), g[f"{tag}_db"], rtol=1e-3, atol=1e-4)
+        if res:
+            np.testing.assert_allclose(rows(r.grad), g[f"{tag}_dr{rank}"], rtol=1e-6, atol=0)
+
+    # against torch's own SyncBatchNorm over NCCL, bf16 and fp32, uneven per-rank batch, many layers in a row
+    for dtype, tol in ((torch.float32, dict(rtol=1e-4, atol=1e-5)), (torch.bfloat16, dict(rtol=2e-2, atol=2e-2))):
+        torch.manual_seed(10 + rank)
+        for it, (n, c, hw) in enumerate([(8 + 4 * rank, 256, 14), (16, 64, 28), (4, 2048, 7), (6 - rank, 512, 7)] * 3):
+            ref = torch.nn.SyncBatchNorm(c).cuda()
+            ours = b200.B200SyncBatchNorm(c).cuda()
+            x = (torch.randn(n, c, hw, hw, device="cuda") * 2 + 1).to(dtype).contiguous(memory_format=torch.channels_last)
+            dy = torch.randn_like(x)
+            xa, xb = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
+            ya, yb = ours(xa), ref(xb)
+            ya.backward(dy); yb.backward(dy)
+            torch.testing.assert_close(ya, yb, **tol)
+            torch.testing.assert_close(xa.grad, xb.grad, rtol=tol["rtol"], atol=tol["atol"] * 4)
+            torch.testing.assert_close(ours.running_mean, ref.running_mean, rtol=1e-4, atol=1e-5)
+            torch.testing.assert_close(ours.running_var, ref.running_var, rtol=1e-3, atol=1e-5)
+            torch.testing.assert_close(ours.weight.grad, ref.weight.grad, rtol=2e-2, atol=2e-2 * hw)
+    from dbx_distributed_pytorch_examples_b200.comm import stats_communicator
+    stats_communicator().check_error()
+    dist.barrier()
+    dist.destroy_process_group()
+    return "ok"
+
+
+def _w_allreduce():
+    import ctypes
+    import math
+    import torch
+    import torch.distributed as dist
+    from dbx_distributed_pytorch_examples_b200 import _lib
+    from dbx_distributed_pytorch_examples_b200.comm import Communicator
+    rank, world = _init()
+    lib = _lib.lib()
+    for dtype, tol in ((torch.float32, dict(rtol=1e-5, atol=1e-6)), (torch.bfloat16, dict(rtol=2e-2, atol=2e-2))):
+        code, es = _lib.dtype_code(dtype), (2 if dtype == torch.bfloat16 else 4)
+        for n, one_shot in [(16, 0), (16, 1), (4096, 1), (1000 * 16, 0), (8 * 1024 * 1024, 0)]:
+            nbytes = (n * es + 511) // 512 * 512
+            comm = Communicator(heap_bytes=2 * nbytes)
+            grad, param = comm.heap_view(0, n, dtype), comm.heap_view(nbytes, n, dtype)
+            torch.manual_seed(7)
+            p0 = torch.randn(n, device="cuda")
+            param.copy_(p0)
+            master = p0.clone() if dtype == torch.bfloat16 else None
+            s1 = torch.zeros(n, device="cuda")
+            ref_p = torch.nn.Parameter(p0.clone())
+            ref_opt = torch.optim.SGD([ref_p], lr=0.1, momentum=0.9)
+            for step in range(3):
+                torch.manual_seed(100 * step + rank)
+                g = torch.randn(n, device="cuda").to(dtype)
+                grad.copy_((g.float() / world).to(dtype))          # what b200dp_bucket_pack leaves there
+                want = (g.float() / world).to(dtype).float()
+                dist.all_reduce(want)                               # NCCL baseline of the same sum
+                torch.cuda.synchronize(); dist.barrier()
+                o = _lib.OptArgs()
+                o.kind, o.lr, o.momentum, o.first_step = _lib.OPT_SGD, 0.1, 0.9, int(step == 0)
+                _lib.check(lib.b200dp_allreduce_update(
+                    comm.handle, 0, code, nbytes, code, 0, n, None if master is None else master.data_ptr(),
+                    s1.data_ptr(), None, ctypes.byref(o), one_shot, 0 if one_shot else 1, 0, comm.next_seq(),
+                    _lib.current_stream()))
+                torch.cuda.synchronize()
+                if not one_shot:                                    # averaged gradient written back everywhere
+                    torch.testing.assert_close(grad.float(), want.to(dtype).float(), **tol)
+                ref_p.grad = want.clone()
+                ref_opt.step()
+                torch.testing.assert_close(param.float(), ref_p.detach().to(dtype).float(), **tol)
+            # every rank holds the same parameters
+            mine = param.float().clone()
+            other = mine.clone()
+            dist.broadcast(other, src=0)
+            assert torch.equal(mine, other), "ranks disagree on the updated parameters"
+            comm.check_error()
+            dist.barrier()
+            comm.destroy()
+    dist.destroy_process_group()
+    return "ok"
+
+
+def _w_ddp_config1(steps):
+    import torch
+    import torch.distributed as dist
+    import torch.nn.functional as F
+    import dbx_distributed_pytorch_examples_b200 as b200
+    from dbx_distributed_pytorch_examples_b200 import workloads
+    rank, world = _init()
+    gold = np.load(os.path.join(GOLD, "ddp_config1.npz"))
+    torch.manual_seed(0)
+    model = workloads.cifar_resnet18(10).cuda()
+    ddp = b200.B200DDP(model, device_ids=[rank], output_device=rank)
+    opt = torch.optim.SGD(ddp.parameters(), lr=1e-3, momentum=0.5)
+    ddp.fuse_optimizer(opt, materialize_grads=True)
+    names = ["fc.weight", "fc.bias", "bn1.weight", "layer1.0.conv1.weight", "layer4.1.bn2.bias"]
+    losses = []
+    for step in range(steps):
+        gen = torch.Generator().manual_seed((100 + rank) * 100000 + step)
+        x = torch.randn(128, 3, 32, 32, generator=gen).cuda()
+        y = torch.randint(0, 10, (128,), generator=gen).cuda()
+        opt.zero_grad()
+        loss = F.cross_entropy(ddp(x), y)
+        loss.backward()
+        opt.step()
+        losses.append(float(loss.detach()))
+        if step == 0:
+            sd = dict(model.named_parameters())
+            for n in names:  # reduced gradients and updated weights of the first step vs stock DDP (CPU, gloo)
+                scale = float(np.abs(gold["grad1_" + n]).max())
+                np.testing.assert_allclose(sd[n].grad.cpu().numpy(), gold["grad1_" + n], rtol=1e-3, atol=2e-5 * scale,
+                                           err_msg=n)
+                np.testing.assert_allclose(sd[n].detach().cpu().numpy(), gold["w1_" + n], rtol=1e-5, atol=1e-6, err_msg=n)
+    want = gold[f"loss_rank{rank}"][:steps]
+    rel = np.abs(np.asarray(losses) - want) / want
+    assert rel.max() < 0.01, f"loss curve deviates by {rel.max():.4f} at step {int(rel.argmax())}"
+    ddp.comm.check_error()
+    dist.barrier()
+    dist.destroy_process_group()
+    return {"max_rel": float(rel.max()), "last": losses[-1]}
+
+
+def _w_ddp_syncbn_vs_torch():
+    """Config 2 in small: SyncBN-converted ResNet-18 under DDP, ours (fused BN+ReLU, fused SGD) against
+    torch's nn.SyncBatchNorm + DistributedDataParallel + SGD over NCCL, same seeds."""
+    import copy
+    import torch
+    import torch.distributed as dist
+    import torch.nn.functional as F
+    import dbx_distributed_pytorch_examples_b200 as b200
+    from dbx_distributed_pytorch_examples_b200 import workloads
+    rank, world = _init()
+    torch.manual_seed(0)
+    base = workloads.cifar_resnet18(10).cuda()
+    ref = torch.nn.parallel.DistributedDataParallel(torch.nn.SyncBatchNorm.convert_sync_batchnorm(copy.deepcopy(base)),
+                                                    device_ids=[rank])
+    ours = b200.B200DDP(b200.fuse_bn_relu(b200.convert_sync_batchnorm(copy.deepcopy(base))), device_ids=[rank])
+    o_ref = torch.optim.SGD(ref.parameters(), lr=1e-2, momentum=0.5)
+    o_our = ours.fuse_optimizer(torch.optim.SGD(ours.parameters(), lr=1e-2, momentum=0.5))
+    for step in range(8):
+        gen = torch.Generator().manual_seed(1000 * rank + step)
+        x = torch.randn(64, 3, 32, 32, generator=gen).cuda()
+        y = torch.randint(0, 10, (64,), generator=gen).cuda()
+        o_ref.zero_grad(); o_our.zero_grad()
+        la = F.cross_entropy(ref(x), y); la.backward(); o_ref.step()
+        lb = F.cross_entropy(ours(x.contiguous(memory_format=torch.channels_last)), y); lb.backward(); o_our.step()
+        assert abs(float(la) - float(lb)) < 2e-3 * float(la), (step, float(la), float(lb))
+    for (n, a), b in zip(ref.module.named_parameters(), ours.module.parameters()):
+        torch.testing.assert_close(b, a, rtol=2e-3, atol=2e-4, msg=lambda s: f"{n}: {s}")
+    torch.testing.assert_close(ours.module.bn1.running_var, ref.module.bn1.running_var, rtol=1e-3, atol=1e-5)
+    dist.barrier()
+    dist.destroy_process_group()
+    return "ok"
+
+
+def test_syncbn_two_ranks():
+    assert TorchDistributor(num_processes=2).run(_w_syncbn) == "ok"
+
+
+def test_fused_allreduce_update_two_ranks():
+    assert TorchDistributor(num_processes=2).run(_w_allreduce) == "ok"
+
+
+def test_config1_loss_curve_two_ranks():
+    out = TorchDistributor(num_processes=2).run(_w_ddp_config1, 200)
+    assert out["max_rel"] < 0.01
+
+
+def test_syncbn_ddp_against_torch_two_ranks():
+    assert TorchDistributor(num_processes=2).run(_w_ddp_syncbn_vs_torch) == "ok"
