@@ -8,6 +8,8 @@
 // same channels for its whole life (their statistics / coefficients stay in
 // registers).  grid = (row splits, channel chunks), one resident wave: 4 CTAs
 // per SM for the forward kernels (<= 64 registers), 3 for the backward ones.
+// Rows are staged through per-thread shared-memory rings filled by cp.async, so
+// each thread has 4-8 rows per input in flight (RowRing below).
 //
 // Reductions (stats, backward sums): thread -> CTA tree in shared memory ->
 // per-CTA partial in `scratch` -> the last CTA of each chunk (ticket counter)
@@ -22,11 +24,14 @@
 // is recomputed from x (mode 1) or read from y (mode 2, +2 B per bwd pass).
 #include <mutex>
 
+#include <cooperative_groups.h>
+
 #include "common.cuh"
 
 namespace {
 
 using namespace b200dp;
+namespace cg = cooperative_groups;
 
 constexpr int kT = 256;           // threads per CTA
 constexpr int kCV = 8;            // 16-byte vectors per chunk row (128 B)
@@ -35,7 +40,8 @@ constexpr int kOccFwd = 4;        // resident CTAs per SM, forward kernels
 constexpr int kOccBwd = 3;        // resident CTAs per SM, backward kernels
 constexpr int kMaxCtas = kOccFwd * B200DP_NUM_SMS;
 constexpr int kMaxPartials = kMaxCtas * 64;  // (row split, channel) pairs
-constexpr int kUnroll = 4;
+constexpr int kUnroll = 4;        // rows per CTA pass assumed by the grid planner
+constexpr int kCluster = 8;       // CTAs per thread-block cluster in the reduction kernels
 
 // scratch layout (bytes): tickets[128] u32 | counts[1024] f32 | pa[kMaxPartials] | pb[kMaxPartials]
 constexpr size_t kScratchTickets = 0;
@@ -58,6 +64,57 @@ Grid2 plan_grid(int64_t M, int C, int occ) {
   if (cap < 1) cap = 1;
   g.gx = (int)(want < 1 ? 1 : (want > cap ? cap : want));
   return g;
+}
+
+// Reduction kernels run in clusters of kCluster CTAs along x (same channel chunk): the
+// row split is a whole number of clusters, and the grid must not exceed the number of
+// clusters the GPU can hold at once (GPC boundaries make that a little less than
+// occupancy * SMs / kCluster: 71 instead of 74 on B200) or a few clusters run as a second
+// wave and double the kernel's duration.
+template <typename T>
+Grid2 plan_grid_clustered(int64_t M, int C, int max_clusters) {
+  Grid2 g = plan_grid<T>(M, C, kOccFwd);
+  int cap = max_clusters / g.gy * kCluster;
+  g.gx = (g.gx + kCluster - 1) / kCluster * kCluster;
+  if (g.gx > cap) g.gx = cap;
+  if (g.gx < kCluster) g.gx = kCluster;
+  return g;
+}
+
+// cudaOccupancyMaxActiveClusters for a kernel of this file, asked once per device.
+template <typename KernelT>
+int max_active_clusters(KernelT kernel) {
+  struct Entry { const void* fn; int dev; int n; };
+  static Entry table[256];  // (kernel, device) -> clusters; racing writers store the same value
+  static int used = 0;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 64;
+  const void* key = reinterpret_cast<const void*>(kernel);
+  for (int i = 0; i < used; ++i)
+    if (table[i].fn == key && table[i].dev == dev) return table[i].n;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(kCluster * B200DP_NUM_SMS, 1, 1);
+  cfg.blockDim = dim3(kT, 1, 1);
+  cfg.dynamicSmemBytes = 0;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = kCluster;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, kernel, &cfg) != cudaSuccess || n <= 0) {
+    cudaGetLastError();
+    n = 64;  // conservative: 8 per GPC
+  }
+  if (used < 256) {
+    table[used].fn = key;
+    table[used].dev = dev;
+    table[used].n = n;
+    ++used;
+  }
+  return n;
 }
 
 // ---- Chan / Welford merge of (na, ma, qa) with (nb, mb, qb), N channels -----
@@ -121,24 +178,62 @@ __device__ __forceinline__ void cta_tree(float* sA, float* sB, float* sN, float&
 }
 
 // After the CTA tree, threads with r == 0 hold the CTA's (n, a[], b[]) for their
-// channels.  Publish the partial, elect the last CTA of this chunk, and let it
-// merge all partials.  Returns true in the electing CTA, where r == 0 threads
-// then hold the chunk's final values.
+// channels.  Stage 1: the kCluster CTAs of a cluster hand their results to the cluster's
+// first CTA through distributed shared memory.  Stage 2: the cluster leaders publish one
+// partial each to `scratch`, elect the last leader of the chunk (ticket), and that CTA
+// merges the partials.  Returns true in that one CTA, where r == 0 threads then hold the
+// chunk's final values.  (592 CTAs leave 74 partials instead of 592: the serial tail of
+// the last CTA is what bounded the reduction kernels before.)
 template <int N, bool WELFORD>
 __device__ __forceinline__ bool grid_merge(void* scratch, int C, int chbase, bool chan_ok,
                                            float* sA, float* sB, float* sN, float& n, float* a,
                                            float* b) {
   __shared__ bool is_last;
+  __shared__ __align__(16) float xchg[kCV][2 * N + 4];  // read by the cluster leader over DSMEM
+  const int tid = threadIdx.x, r = tid / kCV;
+  cg::cluster_group cluster = cg::this_cluster();
+  if (r == 0) {
+#pragma unroll
+    for (int k = 0; k < N; ++k) {
+      xchg[tid][k] = a[k];
+      xchg[tid][N + k] = b[k];
+    }
+    xchg[tid][2 * N] = n;
+  }
+  cluster.sync();
+  const bool leader = cluster.block_rank() == 0;
+  if (leader && r == 0) {
+    for (unsigned q = 1; q < kCluster; ++q) {
+      const float* rem = cluster.map_shared_rank(&xchg[tid][0], q);
+      float oa[N], ob[N];
+#pragma unroll
+      for (int k = 0; k < N; ++k) {
+        oa[k] = rem[k];
+        ob[k] = rem[N + k];
+      }
+      if (WELFORD) {
+        welford_merge<N>(n, a, b, rem[2 * N], oa, ob);
+      } else {
+#pragma unroll
+        for (int k = 0; k < N; ++k) {
+          a[k] += oa[k];
+          b[k] += ob[k];
+        }
+      }
+    }
+  }
+  cluster.sync();  // the others' shared memory must stay alive until the leader has read it
+  if (!leader) return false;
+
   unsigned int* tickets = reinterpret_cast<unsigned int*>((char*)scratch + kScratchTickets);
   float* counts = reinterpret_cast<float*>((char*)scratch + kScratchCounts);
   float* pa = reinterpret_cast<float*>((char*)scratch + kScratchA);
   float* pb = reinterpret_cast<float*>((char*)scratch + kScratchB);
-  const int tid = threadIdx.x, r = tid / kCV;
-  const int bx = blockIdx.x, by = blockIdx.y, gx = gridDim.x;
+  const int bx = blockIdx.x / kCluster, by = blockIdx.y, gx = gridDim.x / kCluster;
   // partial index: (by * gx + bx) * chunk + local channel  (< kMaxPartials by construction)
   const int chunk = kCV * N;
   const int lc = (tid % kCV) * N;
-  if (gx == 1) return true;  // single row split: the CTA result is final
+  if (gx == 1) return true;  // a single cluster per chunk: its result is final
 
   if (r == 0) {
     float* da = pa + ((size_t)by * gx + bx) * chunk + lc;
@@ -227,13 +322,137 @@ __device__ __forceinline__ void wait_chunk(const b200dp_peers& P, uint32_t seq) 
   __syncthreads();
 }
 
-// =============================== forward: stats ===============================
+// ---- per-thread staging ring in shared memory -------------------------------
+// Each thread owns D slots of 16 bytes per input stream and fills them with
+// cp.async (LDGSTS): the loads of its next D rows are in flight while it works on
+// the current one, at no cost in registers.  Slots are private to the thread, so
+// the only synchronisation is cp.async.wait_group.  With 3-4 CTAs per SM this
+// keeps 100-150 KB of requests per SM outstanding, which is what the HBM3e
+// latency-bandwidth product asks for (~45-65 KB per SM at 6.5 TB/s).
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async16_evict_first(uint32_t dst, const void* src, uint64_t pol) {
+  asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(dst), "l"(src),
+               "l"(pol)
+               : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 r;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "r"(addr));
+  return r;
+}
+
+// rows this thread owns: first row, distance between its rows, how many
+struct RowRange {
+  int64_t first, step;
+  int count;
+};
+__device__ __forceinline__ RowRange my_rows(int64_t M, int r) {
+  RowRange rr;
+  rr.step = (int64_t)gridDim.x * kRows;
+  rr.first = (int64_t)blockIdx.x * kRows + r;
+  rr.count = rr.first < M ? (int)((M - rr.first + rr.step - 1) / rr.step) : 0;
+  return rr;
+}
+
+template <int D, int NS, bool EVICT_FIRST>
+struct RowRing {
+  uint32_t base;  // shared-space address of this thread's slot (stream 0, depth 0)
+  uint64_t pol;
+  __device__ __forceinline__ void init(void* smem) {
+    base = (uint32_t)__cvta_generic_to_shared(smem) + threadIdx.x * 16;
+    if (EVICT_FIRST) pol = evict_first_policy();
+  }
+  __device__ __forceinline__ uint32_t slot(int d, int s) const { return base + (s * D + d) * (kT * 16); }
+  __device__ __forceinline__ void issue(int d, const void* p0, const void* p1, const void* p2) {
+    if (EVICT_FIRST) {
+      cp_async16_evict_first(slot(d, 0), p0, pol);
+      if (NS > 1) cp_async16_evict_first(slot(d, 1), p1, pol);
+      if (NS > 2) cp_async16_evict_first(slot(d, 2), p2, pol);
+    } else {
+      cp_async16(slot(d, 0), p0);
+      if (NS > 1) cp_async16(slot(d, 1), p1);
+      if (NS > 2) cp_async16(slot(d, 2), p2);
+    }
+  }
+  // Fill the ring with the first rows; one commit group per row, always D groups.
+  template <typename PtrF>
+  __device__ __forceinline__ void prime(int nrows, PtrF ptrs) {
+#pragma unroll
+    for (int k = 0; k < D; ++k) {
+      if (k < nrows) {
+        const void *p0, *p1, *p2;
+        ptrs(k, p0, p1, p2);
+        issue(k, p0, p1, p2);
+      }
+      cp_async_commit();
+    }
+  }
+  // proc(k, v0, v1, v2) for k = 0 … nrows-1 in order; refills the slot it has just drained.
+  template <typename PtrF, typename ProcF>
+  __device__ __forceinline__ void run(int nrows, PtrF ptrs, ProcF proc) {
+    int d = 0;
+    for (int k = 0; k < nrows; ++k) {
+      cp_async_wait<D - 1>();  // the group of row k has landed
+      uint4 v0 = lds128(slot(d, 0)), v1, v2;
+      if (NS > 1) v1 = lds128(slot(d, 1));
+      if (NS > 2) v2 = lds128(slot(d, 2));
+      proc(k, v0, v1, v2);     // consumes the values: the slot may be overwritten after this
+      if (k + D < nrows) {
+        const void *p0, *p1, *p2;
+        ptrs(k + D, p0, p1, p2);
+        issue(d, p0, p1, p2);
+      }
+      cp_async_commit();
+      d = (d + 1 == D) ? 0 : d + 1;
+    }
+    cp_async_wait<0>();
+  }
+  static constexpr int kBytes = D * NS * kT * 16;
+};
+
+
+// per-channel vectors: N consecutive floats, 16-byte aligned
+template <int N>
+__device__ __forceinline__ void ldg_vec(const float* p, float* out) {
+#pragma unroll
+  for (int k = 0; k < N; k += 4) {
+    const float4 v = *reinterpret_cast<const float4*>(p + k);
+    out[k] = v.x; out[k + 1] = v.y; out[k + 2] = v.z; out[k + 3] = v.w;
+  }
+}
+template <int N>
+__device__ __forceinline__ void sts_vec(float* p, const float* in) {
+#pragma unroll
+  for (int k = 0; k < N; k += 4) *reinterpret_cast<float4*>(p + k) = make_float4(in[k], in[k + 1], in[k + 2], in[k + 3]);
+}
 template <typename T>
-__global__ void __launch_bounds__(kT, kOccFwd)
+struct is_bf16 { static constexpr bool value = false; };
+template <>
+struct is_bf16<__nv_bfloat16> { static constexpr bool value = true; };
+
+// =============================== forward: stats ===============================
+constexpr int kDepthStats = 8;
+
+template <typename T>
+__global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kT, kOccFwd)
 bn_stats_kernel(const T* __restrict__ x, int64_t M, int C, void* scratch, float* stats_local,
                 b200dp_peers P, uint32_t seq) {
   constexpr int N = Vec<T>::N;
-  __shared__ float sA[N * kT], sB[N * kT], sN[kT];
+  using Ring = RowRing<kDepthStats, 1, false>;
+  constexpr int kTreeBytes = (2 * N * kT + kT) * 4;
+  __shared__ __align__(16) unsigned char smem[Ring::kBytes > kTreeBytes ? Ring::kBytes : kTreeBytes];
+  float* sA = reinterpret_cast<float*>(smem);  // the reduction tree reuses the ring once it is drained
+  float* sB = sA + N * kT;
+  float* sN = sB + N * kT;
   const int tid = threadIdx.x, r = tid / kCV, cv = tid % kCV;
   const int c0 = blockIdx.y * (kCV * N) + cv * N;
   const bool chan_ok = c0 < C;
@@ -243,32 +462,56 @@ bn_stats_kernel(const T* __restrict__ x, int64_t M, int C, void* scratch, float*
   for (int k = 0; k < N; ++k) mean[k] = m2[k] = 0.f;
 
   if (chan_ok) {
-    const int64_t stride = (int64_t)gridDim.x * kRows;
-    for (int64_t row0 = (int64_t)blockIdx.x * kRows + r; row0 < M; row0 += kUnroll * stride) {
-      uint4 v[kUnroll];
+    const RowRange rr = my_rows(M, r);
+    const T* base = x + rr.first * C + c0;
+    const int64_t step = rr.step * C;
+    auto ptrs = [&](int k, const void*& p0, const void*& p1, const void*& p2) {
+      p0 = base + k * step;
+      p1 = p2 = nullptr;
+    };
+    auto proc = [&](int, const uint4& v, const uint4&, const uint4&) {
+      if constexpr (is_bf16<T>::value) {
+        // bf16 rows: raw first and second moments with FHADD/FHFMA (2 instructions per
+        // element, products exact in fp32); turned into (mean, M2) once per thread below
+        // and merged from there on with Chan's formula.  A thread owns at most a few
+        // hundred rows, so the single-pass cancellation stays far below bf16's own step.
 #pragma unroll
-      for (int u = 0; u < kUnroll; ++u) {
-        const int64_t row = row0 + u * stride;
-        if (row < M) v[u] = ld_keep(x + row * C + c0);
+        for (int k = 0; k < N; ++k) {
+          const uint16_t h = vec_half(v, k);
+          mean[k] = add_bf16_f32(h, mean[k]);      // running sum
+          m2[k] = fma_bf16_f32(h, h, m2[k]);       // running sum of squares
+        }
+      } else {
+        float f[N];
+        Vec<T>::unpack(v, f);
+        n += 1.f;
+        const float rn = __frcp_rn(n);
+#pragma unroll
+        for (int k = 0; k < N; ++k) {
+          const float d = f[k] - mean[k];
+          mean[k] = fmaf(d, rn, mean[k]);
+          m2[k] = fmaf(d, f[k] - mean[k], m2[k]);
+        }
       }
+    };
+    Ring ring;
+    ring.init(smem);
+    ring.prime(rr.count, ptrs);
+    ring.run(rr.count, ptrs, proc);
+    if constexpr (is_bf16<T>::value) {
+      n = (float)rr.count;
+      if (rr.count > 0) {
+        const float rn = 1.0f / n;
 #pragma unroll
-      for (int u = 0; u < kUnroll; ++u) {
-        const int64_t row = row0 + u * stride;
-        if (row < M) {
-          float f[N];
-          Vec<T>::unpack(v[u], f);
-          n += 1.f;
-          const float rn = __frcp_rn(n);
-#pragma unroll
-          for (int k = 0; k < N; ++k) {
-            const float d = f[k] - mean[k];
-            mean[k] = fmaf(d, rn, mean[k]);
-            m2[k] = fmaf(d, f[k] - mean[k], m2[k]);
-          }
+        for (int k = 0; k < N; ++k) {
+          const float s = mean[k];
+          mean[k] = s * rn;
+          m2[k] = fmaxf(fmaf(-s, mean[k], m2[k]), 0.f);
         }
       }
     }
   }
+  __syncthreads();  // every thread is done with its ring slots before the tree overwrites them
   cta_tree<N, true>(sA, sB, sN, n, mean, m2);
   if (!grid_merge<N, true>(scratch, C, c0, chan_ok, sA, sB, sN, n, mean, m2)) return;
 
@@ -304,17 +547,44 @@ struct FwdArgs {
   const float* given_var;
 };
 
+// Per-channel coefficients of one chunk are worked out once per CTA, by its first kCV
+// threads (one 16-byte channel group each), and handed to the other 31 rows of threads
+// through shared memory: a small layer gives every thread only a handful of rows, and
+// 256 threads each redoing the divisions and square roots cost more than the rows.
+constexpr int kChunkMax = kCV * 8;  // channels per chunk at most (bf16)
+
 template <typename T, bool RELU, bool RES>
-__global__ void __launch_bounds__(kT, RES ? kOccBwd : kOccFwd) bn_fwd_apply_kernel(FwdArgs A, b200dp_peers P, uint32_t seq) {
+__global__ void __launch_bounds__(kT, kOccFwd) bn_fwd_apply_kernel(FwdArgs A, b200dp_peers P, uint32_t seq) {
   constexpr int N = Vec<T>::N;
+  using Ring = RowRing<RES ? 4 : 8, RES ? 2 : 1, true>;
+  __shared__ __align__(16) unsigned char smem[Ring::kBytes];
+  __shared__ __align__(16) float coef[3][kChunkMax];  // -mean, a = invstd*weight, b = bias
   const int tid = threadIdx.x, r = tid / kCV, cv = tid % kCV;
   const int C = A.C;
   const int c0 = blockIdx.y * (kCV * N) + cv * N;
   const bool chan_ok = c0 < C;
 
-  float mean[N], a[N], b[N];
-  if (A.given_mean) {
-    if (chan_ok) {
+  // Start streaming now: the first rows fly while the flags are awaited and the
+  // coefficients are computed below.
+  const T* xb = static_cast<const T*>(A.x);
+  const T* rb = static_cast<const T*>(A.res);
+  T* yb = static_cast<T*>(A.y);
+  const RowRange rr = my_rows(A.M, r);
+  const int64_t off0 = rr.first * C + c0, step = rr.step * C;
+  auto ptrs = [&](int k, const void*& p0, const void*& p1, const void*& p2) {
+    p0 = xb + off0 + k * step;
+    p1 = RES ? (const void*)(rb + off0 + k * step) : nullptr;
+    p2 = nullptr;
+  };
+  Ring ring;
+  ring.init(smem);
+  const int nrows = chan_ok ? rr.count : 0;
+  ring.prime(nrows, ptrs);
+
+  if (!A.given_mean && P.world > 1) wait_chunk(P, seq);
+  if (tid < kCV && chan_ok) {  // r == 0: this thread's c0 is the group it publishes
+    float mean[N], a[N], b[N];
+    if (A.given_mean) {
 #pragma unroll
       for (int k = 0; k < N; ++k) {
         mean[k] = A.given_mean[c0 + k];
@@ -322,14 +592,11 @@ __global__ void __launch_bounds__(kT, RES ? kOccBwd : kOccFwd) bn_fwd_apply_kern
         a[k] = invstd * (A.weight ? A.weight[c0 + k] : 1.f);
         b[k] = A.bias ? A.bias[c0 + k] : 0.f;
       }
-    }
-  } else {
-    float n = 0.f, m2[N];
+    } else {
+      float n = 0.f, m2[N];
 #pragma unroll
-    for (int k = 0; k < N; ++k) mean[k] = m2[k] = 0.f;
-    if (P.world > 1) {
-      wait_chunk(P, seq);
-      if (chan_ok) {
+      for (int k = 0; k < N; ++k) mean[k] = m2[k] = 0.f;
+      if (P.world > 1) {
         const int slot = seq % B200DP_XCHG_SLOTS;
         for (int p = 0; p < P.world; ++p) {
           const float* d = P.sync[P.rank]->bn_data[slot][p];
@@ -342,19 +609,17 @@ __global__ void __launch_bounds__(kT, RES ? kOccBwd : kOccFwd) bn_fwd_apply_kern
           const float on = ld_cg_f32(d + 2 * B200DP_BN_MAX_CHANNELS + blockIdx.y);
           welford_merge<N>(n, mean, m2, on, om, oq);
         }
-      }
-    } else if (chan_ok) {
-      n = ld_cg_f32(A.stats_local + 2 * C);
+      } else {
+        n = ld_cg_f32(A.stats_local + 2 * C);
 #pragma unroll
-      for (int k = 0; k < N; ++k) {
-        mean[k] = ld_cg_f32(A.stats_local + c0 + k);
-        m2[k] = ld_cg_f32(A.stats_local + C + c0 + k);
+        for (int k = 0; k < N; ++k) {
+          mean[k] = ld_cg_f32(A.stats_local + c0 + k);
+          m2[k] = ld_cg_f32(A.stats_local + C + c0 + k);
+        }
       }
-    }
-    if (chan_ok) {
       const float inv_n = n > 0.f ? 1.0f / n : 0.f;
       const float inv_nm1 = n > 1.f ? 1.0f / (n - 1.f) : 0.f;
-      const bool writer = (blockIdx.x == 0) && (r == 0);
+      const bool writer = blockIdx.x == 0;
 #pragma unroll
       for (int k = 0; k < N; ++k) {
         const float var = m2[k] * inv_n;
@@ -374,104 +639,138 @@ __global__ void __launch_bounds__(kT, RES ? kOccBwd : kOccFwd) bn_fwd_apply_kern
       }
       if (writer && tid == 0 && blockIdx.y == 0) A.save_count[0] = n;
     }
+#pragma unroll
+    for (int k = 0; k < N; ++k) mean[k] = -mean[k];
+    sts_vec<N>(&coef[0][cv * N], mean);
+    sts_vec<N>(&coef[1][cv * N], a);
+    sts_vec<N>(&coef[2][cv * N], b);
   }
-  if (!chan_ok) return;
+  __syncthreads();
+  float nmean[N], a[N], b[N];
+  ldg_vec<N>(&coef[0][cv * N], nmean);  // (generic loads from shared memory)
+  ldg_vec<N>(&coef[1][cv * N], a);
+  ldg_vec<N>(&coef[2][cv * N], b);
 
-  const T* x = static_cast<const T*>(A.x);
-  const T* res = static_cast<const T*>(A.res);
-  T* y = static_cast<T*>(A.y);
-  const int64_t M = A.M;
-  const int64_t stride = (int64_t)gridDim.x * kRows;
-  for (int64_t row0 = (int64_t)blockIdx.x * kRows + r; row0 < M; row0 += kUnroll * stride) {
-    uint4 v[kUnroll], w[kUnroll];
+  auto proc = [&](int k, const uint4& vx, const uint4& vr, const uint4&) {
+    float f[N];
+    if constexpr (is_bf16<T>::value) {
 #pragma unroll
-    for (int u = 0; u < kUnroll; ++u) {
-      const int64_t row = row0 + u * stride;
-      if (row < M) {
-        v[u] = ld_stream(x + row * C + c0);
-        if (RES) w[u] = ld_stream(res + row * C + c0);
+      for (int j = 0; j < N; ++j) {
+        float o = fmaf(add_bf16_f32(vec_half(vx, j), nmean[j]), a[j], b[j]);
+        if (RES) o = add_bf16_f32(vec_half(vr, j), o);
+        f[j] = RELU ? fmaxf(o, 0.f) : o;
+      }
+    } else {
+      float g[N];
+      Vec<T>::unpack(vx, f);
+      if (RES) Vec<T>::unpack(vr, g);
+#pragma unroll
+      for (int j = 0; j < N; ++j) {
+        float o = fmaf(f[j] + nmean[j], a[j], b[j]);
+        if (RES) o += g[j];
+        f[j] = RELU ? fmaxf(o, 0.f) : o;
       }
     }
-#pragma unroll
-    for (int u = 0; u < kUnroll; ++u) {
-      const int64_t row = row0 + u * stride;
-      if (row < M) {
-        float f[N], g[N];
-        Vec<T>::unpack(v[u], f);
-        if (RES) Vec<T>::unpack(w[u], g);
-#pragma unroll
-        for (int k = 0; k < N; ++k) {
-          float o = fmaf(f[k] - mean[k], a[k], b[k]);
-          if (RES) o += g[k];
-          if (RELU) o = fmaxf(o, 0.f);
-          f[k] = o;
-        }
-        // y is read again by the next convolution: leave it in L2
-        *reinterpret_cast<uint4*>(y + row * C + c0) = Vec<T>::pack(f);
-      }
-    }
-  }
+    // y is read again by the next convolution: leave it in L2
+    *reinterpret_cast<uint4*>(yb + off0 + k * step) = Vec<T>::pack(f);
+  };
+  ring.run(nrows, ptrs, proc);
 }
 
 // ============================= backward: reduce ==============================
 // RELU: 0 none, 1 mask recomputed from x (no residual was fused), 2 mask from y.
 template <typename T, int RELU>
-__global__ void __launch_bounds__(kT, kOccBwd)
+__global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kT, kOccFwd)
 bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T* __restrict__ yo,
                      int64_t M, int C, const float* save_mean, const float* save_invstd,
                      const float* weight, const float* bias, void* scratch, float* sums_local,
                      float* grad_weight, float* grad_bias, b200dp_peers P, uint32_t seq) {
   constexpr int N = Vec<T>::N;
-  __shared__ float sA[N * kT], sB[N * kT];
+  using Ring = RowRing<RELU == 2 ? 3 : 4, RELU == 2 ? 3 : 2, false>;  // 32 or 36 KiB (static smem limit 48 KiB)
+  constexpr int kTreeBytes = 2 * N * kT * 4;
+  __shared__ __align__(16) unsigned char smem[Ring::kBytes > kTreeBytes ? Ring::kBytes : kTreeBytes];
+  float* sA = reinterpret_cast<float*>(smem);
+  float* sB = sA + N * kT;
   const int tid = threadIdx.x, r = tid / kCV, cv = tid % kCV;
   const int c0 = blockIdx.y * (kCV * N) + cv * N;
   const bool chan_ok = c0 < C;
 
-  float mean[N], a[N], b[N], s1[N], s2[N];
+  float s1[N], s2[N];
 #pragma unroll
   for (int k = 0; k < N; ++k) s1[k] = s2[k] = 0.f;
   if (chan_ok) {
+    const RowRange rr = my_rows(M, r);
+    const int64_t off0 = rr.first * C + c0, step = rr.step * C;
+    auto ptrs = [&](int k, const void*& p0, const void*& p1, const void*& p2) {
+      p0 = dy + off0 + k * step;
+      p1 = x + off0 + k * step;
+      p2 = RELU == 2 ? (const void*)(yo + off0 + k * step) : nullptr;
+    };
+    Ring ring;
+    ring.init(smem);
+    ring.prime(rr.count, ptrs);  // in flight while the coefficients are fetched
+    float mean[N], nmean[N], a[N], b[N];
+    ldg_vec<N>(save_mean + c0, mean);
 #pragma unroll
-    for (int k = 0; k < N; ++k) {
-      mean[k] = save_mean[c0 + k];
-      if (RELU == 1) {
-        a[k] = save_invstd[c0 + k] * (weight ? weight[c0 + k] : 1.f);
-        b[k] = bias ? bias[c0 + k] : 0.f;
+    for (int k = 0; k < N; ++k) nmean[k] = -mean[k];
+    if (RELU == 1) {
+      ldg_vec<N>(save_invstd + c0, a);
+#pragma unroll
+      for (int k = 0; k < N; ++k) b[k] = 0.f;
+      if (weight) {
+        float w[N];
+        ldg_vec<N>(weight + c0, w);
+#pragma unroll
+        for (int k = 0; k < N; ++k) a[k] *= w[k];
       }
+      if (bias) ldg_vec<N>(bias + c0, b);
     }
-    const int64_t stride = (int64_t)gridDim.x * kRows;
-    for (int64_t row0 = (int64_t)blockIdx.x * kRows + r; row0 < M; row0 += kUnroll * stride) {
-      uint4 vg[kUnroll], vx[kUnroll], vy[kUnroll];
-#pragma unroll
-      for (int u = 0; u < kUnroll; ++u) {
-        const int64_t row = row0 + u * stride;
-        if (row < M) {
-          vg[u] = ld_keep(dy + row * C + c0);
-          vx[u] = ld_keep(x + row * C + c0);
-          if (RELU == 2) vy[u] = ld_keep(yo + row * C + c0);
+    auto proc = [&](int, const uint4& vg, const uint4& vx, const uint4& vy) {
+      if constexpr (is_bf16<T>::value) {
+        // s2 accumulates sum g*x (both bf16: one FHFMA, exact product); the mean is taken
+        // out once at the end: sum g*(x-mean) = sum g*x - mean * sum g.
+        uint4 g = vg;
+        if (RELU == 2) {  // g *= (y > 0), two elements per instruction, exact
+          g.x = bf16x2_mul(vg.x, bf16x2_gt0_mask(vy.x));
+          g.y = bf16x2_mul(vg.y, bf16x2_gt0_mask(vy.y));
+          g.z = bf16x2_mul(vg.z, bf16x2_gt0_mask(vy.z));
+          g.w = bf16x2_mul(vg.w, bf16x2_gt0_mask(vy.w));
         }
-      }
 #pragma unroll
-      for (int u = 0; u < kUnroll; ++u) {
-        const int64_t row = row0 + u * stride;
-        if (row < M) {
-          float g[N], f[N], o[N];
-          Vec<T>::unpack(vg[u], g);
-          Vec<T>::unpack(vx[u], f);
-          if (RELU == 2) Vec<T>::unpack(vy[u], o);
-#pragma unroll
-          for (int k = 0; k < N; ++k) {
-            const float xm = f[k] - mean[k];
-            float gk = g[k];
-            if (RELU == 1) gk = fmaf(xm, a[k], b[k]) > 0.f ? gk : 0.f;
-            if (RELU == 2) gk = o[k] > 0.f ? gk : 0.f;
-            s1[k] += gk;
-            s2[k] = fmaf(gk, xm, s2[k]);
+        for (int k = 0; k < N; ++k) {
+          const uint16_t gh = vec_half(g, k), xh = vec_half(vx, k);
+          if (RELU == 1) {
+            const bool on = fmaf(add_bf16_f32(xh, nmean[k]), a[k], b[k]) > 0.f;
+            s1[k] = on ? add_bf16_f32(gh, s1[k]) : s1[k];
+            s2[k] = on ? fma_bf16_f32(gh, xh, s2[k]) : s2[k];
+          } else {
+            s1[k] = add_bf16_f32(gh, s1[k]);
+            s2[k] = fma_bf16_f32(gh, xh, s2[k]);
           }
         }
+      } else {
+        float g[N], f[N], o[N];
+        Vec<T>::unpack(vg, g);
+        Vec<T>::unpack(vx, f);
+        if (RELU == 2) Vec<T>::unpack(vy, o);
+#pragma unroll
+        for (int k = 0; k < N; ++k) {
+          const float xm = f[k] + nmean[k];
+          float gk = g[k];
+          if (RELU == 1) gk = fmaf(xm, a[k], b[k]) > 0.f ? gk : 0.f;
+          if (RELU == 2) gk = o[k] > 0.f ? gk : 0.f;
+          s1[k] += gk;
+          s2[k] = fmaf(gk, xm, s2[k]);
+        }
       }
+    };
+    ring.run(rr.count, ptrs, proc);
+    if constexpr (is_bf16<T>::value) {
+#pragma unroll
+      for (int k = 0; k < N; ++k) s2[k] = fmaf(nmean[k], s1[k], s2[k]);
     }
   }
+  __syncthreads();  // ring drained everywhere before the tree reuses the memory
   float dummy = 0.f;
   cta_tree<N, false>(sA, sB, nullptr, dummy, s1, s2);
   if (!grid_merge<N, false>(scratch, C, c0, chan_ok, sA, sB, nullptr, dummy, s1, s2)) return;
@@ -508,18 +807,37 @@ struct BwdArgs {
 template <typename T, int RELU, bool DRES>
 __global__ void __launch_bounds__(kT, kOccBwd) bn_bwd_apply_kernel(BwdArgs A, b200dp_peers P, uint32_t seq) {
   constexpr int N = Vec<T>::N;
-  constexpr int U = N == 8 ? 2 : kUnroll;  // 40 coefficient registers at N = 8: fewer rows in flight
+  using Ring = RowRing<RELU == 2 ? 3 : 4, RELU == 2 ? 3 : 2, true>;
+  __shared__ __align__(16) unsigned char smem[Ring::kBytes];
+  __shared__ __align__(16) float coef[5][kChunkMax];  // -mean, a, b, -mean_dy, -k
   const int tid = threadIdx.x, r = tid / kCV, cv = tid % kCV;
   const int C = A.C;
   const int c0 = blockIdx.y * (kCV * N) + cv * N;
   const bool chan_ok = c0 < C;
 
-  float s1[N], s2[N];
+  const T* dyb = static_cast<const T*>(A.dy);
+  const T* xb = static_cast<const T*>(A.x);
+  const T* yob = static_cast<const T*>(A.yo);
+  T* dxb = static_cast<T*>(A.dx);
+  T* dresb = static_cast<T*>(A.dres);
+  const RowRange rr = my_rows(A.M, r);
+  const int64_t off0 = rr.first * C + c0, step = rr.step * C;
+  auto ptrs = [&](int k, const void*& p0, const void*& p1, const void*& p2) {
+    p0 = dyb + off0 + k * step;
+    p1 = xb + off0 + k * step;
+    p2 = RELU == 2 ? (const void*)(yob + off0 + k * step) : nullptr;
+  };
+  Ring ring;
+  ring.init(smem);
+  const int nrows = chan_ok ? rr.count : 0;
+  ring.prime(nrows, ptrs);  // in flight during the flag wait and the prologue
+
+  if (P.world > 1) wait_chunk(P, seq);
+  if (tid < kCV && chan_ok) {
+    float s1[N], s2[N];
 #pragma unroll
-  for (int k = 0; k < N; ++k) s1[k] = s2[k] = 0.f;
-  if (P.world > 1) {
-    wait_chunk(P, seq);
-    if (chan_ok) {
+    for (int k = 0; k < N; ++k) s1[k] = s2[k] = 0.f;
+    if (P.world > 1) {
       const int slot = seq % B200DP_XCHG_SLOTS;
       for (int p = 0; p < P.world; ++p) {
         const float* d = P.sync[P.rank]->bn_data[slot][p];
@@ -529,71 +847,86 @@ __global__ void __launch_bounds__(kT, kOccBwd) bn_bwd_apply_kernel(BwdArgs A, b2
           s2[k] += ld_cg_f32(d + C + c0 + k);
         }
       }
-    }
-  } else if (chan_ok) {
+    } else {
 #pragma unroll
-    for (int k = 0; k < N; ++k) {
-      s1[k] = ld_cg_f32(A.sums_local + c0 + k);
-      s2[k] = ld_cg_f32(A.sums_local + C + c0 + k);
+      for (int k = 0; k < N; ++k) {
+        s1[k] = ld_cg_f32(A.sums_local + c0 + k);
+        s2[k] = ld_cg_f32(A.sums_local + C + c0 + k);
+      }
     }
-  }
-  if (!chan_ok) return;
-
-  float mean[N], a[N], b[N], mdy[N], kx[N];
-  {
     const float cnt = ld_cg_f32(A.save_count);
     const float inv_cnt = cnt > 0.f ? 1.0f / cnt : 0.f;
+    float nmean[N], a[N], b[N], nmdy[N], nkx[N];
 #pragma unroll
     for (int k = 0; k < N; ++k) {
       const float invstd = A.save_invstd[c0 + k];
-      mean[k] = A.save_mean[c0 + k];
+      nmean[k] = -A.save_mean[c0 + k];
       a[k] = invstd * (A.weight ? A.weight[c0 + k] : 1.f);
       b[k] = A.bias ? A.bias[c0 + k] : 0.f;
-      mdy[k] = s1[k] * inv_cnt;
-      kx[k] = s2[k] * inv_cnt * invstd * invstd;
+      nmdy[k] = -(s1[k] * inv_cnt);
+      nkx[k] = -(s2[k] * inv_cnt * invstd * invstd);
     }
+    sts_vec<N>(&coef[0][cv * N], nmean);
+    sts_vec<N>(&coef[1][cv * N], a);
+    sts_vec<N>(&coef[2][cv * N], b);
+    sts_vec<N>(&coef[3][cv * N], nmdy);
+    sts_vec<N>(&coef[4][cv * N], nkx);
   }
+  __syncthreads();
+  float nmean[N], a[N], b[N], nmdy[N], nkx[N];
+  ldg_vec<N>(&coef[0][cv * N], nmean);
+  ldg_vec<N>(&coef[1][cv * N], a);
+  if (RELU == 1) ldg_vec<N>(&coef[2][cv * N], b);
+  ldg_vec<N>(&coef[3][cv * N], nmdy);
+  ldg_vec<N>(&coef[4][cv * N], nkx);
 
-  const T* dy = static_cast<const T*>(A.dy);
-  const T* x = static_cast<const T*>(A.x);
-  const T* yo = static_cast<const T*>(A.yo);
-  T* dx = static_cast<T*>(A.dx);
-  T* dres = static_cast<T*>(A.dres);
-  const int64_t M = A.M;
-  const int64_t stride = (int64_t)gridDim.x * kRows;
-  for (int64_t row0 = (int64_t)blockIdx.x * kRows + r; row0 < M; row0 += U * stride) {
-    uint4 vg[U], vx[U], vy[U];
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int64_t row = row0 + u * stride;
-      if (row < M) {
-        vg[u] = ld_stream(dy + row * C + c0);
-        vx[u] = ld_stream(x + row * C + c0);
-        if (RELU == 2) vy[u] = ld_stream(yo + row * C + c0);
+  // dx = (g - mean_dy - (x-mean)*k) * a   with k = invstd^2 * sum(g*(x-mean)) / count
+  auto proc = [&](int k, const uint4& vg, const uint4& vx, const uint4& vy) {
+    float f[N];
+    if constexpr (is_bf16<T>::value) {
+      uint4 g = vg;
+      if (RELU == 2) {
+        g.x = bf16x2_mul(vg.x, bf16x2_gt0_mask(vy.x));
+        g.y = bf16x2_mul(vg.y, bf16x2_gt0_mask(vy.y));
+        g.z = bf16x2_mul(vg.z, bf16x2_gt0_mask(vy.z));
+        g.w = bf16x2_mul(vg.w, bf16x2_gt0_mask(vy.w));
       }
-    }
+      float gm[N];
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int64_t row = row0 + u * stride;
-      if (row < M) {
-        float g[N], f[N], o[N];
-        Vec<T>::unpack(vg[u], g);
-        Vec<T>::unpack(vx[u], f);
-        if (RELU == 2) Vec<T>::unpack(vy[u], o);
-#pragma unroll
-        for (int k = 0; k < N; ++k) {
-          const float xm = f[k] - mean[k];
-          float gk = g[k];
-          if (RELU == 1) gk = fmaf(xm, a[k], b[k]) > 0.f ? gk : 0.f;
-          if (RELU == 2) gk = o[k] > 0.f ? gk : 0.f;
-          g[k] = gk;
-          f[k] = (gk - mdy[k] - xm * kx[k]) * a[k];
+      for (int j = 0; j < N; ++j) {
+        const float xm = add_bf16_f32(vec_half(vx, j), nmean[j]);
+        float t = add_bf16_f32(vec_half(g, j), nmdy[j]);
+        if (RELU == 1) {
+          const bool on = fmaf(xm, a[j], b[j]) > 0.f;
+          t = on ? t : nmdy[j];
+          if (DRES) gm[j] = on ? add_bf16_f32(vec_half(g, j), 0.f) : 0.f;
         }
-        *reinterpret_cast<uint4*>(dx + row * C + c0) = Vec<T>::pack(f);
-        if (DRES) *reinterpret_cast<uint4*>(dres + row * C + c0) = Vec<T>::pack(g);
+        f[j] = fmaf(xm, nkx[j], t) * a[j];
       }
+      *reinterpret_cast<uint4*>(dxb + off0 + k * step) = Vec<T>::pack(f);
+      if (DRES) {
+        if (RELU == 1) *reinterpret_cast<uint4*>(dresb + off0 + k * step) = Vec<T>::pack(gm);
+        else *reinterpret_cast<uint4*>(dresb + off0 + k * step) = g;  // already masked, already bf16
+      }
+    } else {
+      float g[N], o[N];
+      Vec<T>::unpack(vg, g);
+      Vec<T>::unpack(vx, f);
+      if (RELU == 2) Vec<T>::unpack(vy, o);
+#pragma unroll
+      for (int j = 0; j < N; ++j) {
+        const float xm = f[j] + nmean[j];
+        float gk = g[j];
+        if (RELU == 1) gk = fmaf(xm, a[j], b[j]) > 0.f ? gk : 0.f;
+        if (RELU == 2) gk = o[j] > 0.f ? gk : 0.f;
+        g[j] = gk;
+        f[j] = fmaf(xm, nkx[j], gk + nmdy[j]) * a[j];
+      }
+      *reinterpret_cast<uint4*>(dxb + off0 + k * step) = Vec<T>::pack(f);
+      if (DRES) *reinterpret_cast<uint4*>(dresb + off0 + k * step) = Vec<T>::pack(g);
     }
-  }
+  };
+  ring.run(nrows, ptrs, proc);
 }
 
 // ================================ host side ==================================
@@ -632,11 +965,11 @@ extern "C" int b200dp_bn_fwd_stats(const void* x, int dtype, int64_t M, int C, v
   const b200dp_peers P = b200dp_make_peers(comm);
   cudaStream_t s = (cudaStream_t)stream;
   if (dtype == B200DP_BF16) {
-    const Grid2 g = plan_grid<__nv_bfloat16>(M, C, kOccFwd);
+    const Grid2 g = plan_grid_clustered<__nv_bfloat16>(M, C, max_active_clusters(bn_stats_kernel<__nv_bfloat16>));
     bn_stats_kernel<__nv_bfloat16><<<dim3(g.gx, g.gy), kT, 0, s>>>(
         static_cast<const __nv_bfloat16*>(x), M, C, scratch, stats_local, P, seq);
   } else {
-    const Grid2 g = plan_grid<float>(M, C, kOccFwd);
+    const Grid2 g = plan_grid_clustered<float>(M, C, max_active_clusters(bn_stats_kernel<float>));
     bn_stats_kernel<float><<<dim3(g.gx, g.gy), kT, 0, s>>>(static_cast<const float*>(x), M, C,
                                                            scratch, stats_local, P, seq);
   }
@@ -695,12 +1028,12 @@ extern "C" int b200dp_bn_fwd_stats_noalloc(const void* x, int dtype, int64_t M, 
   const b200dp_peers P = b200dp_make_peers(nullptr);
   Grid2 g;
   if (dtype == B200DP_BF16) {
-    g = plan_grid<__nv_bfloat16>(M, C, kOccFwd);
+    g = plan_grid_clustered<__nv_bfloat16>(M, C, max_active_clusters(bn_stats_kernel<__nv_bfloat16>));
     if ((size_t)g.gx * g.gy * kCV * Vec<__nv_bfloat16>::N > (size_t)kMaxPartials) return B200DP_ETOOBIG;
     bn_stats_kernel<__nv_bfloat16><<<dim3(g.gx, g.gy), kT, 0, s>>>(
         static_cast<const __nv_bfloat16*>(x), M, C, scratch, stats_local, P, 0);
   } else {
-    g = plan_grid<float>(M, C, kOccFwd);
+    g = plan_grid_clustered<float>(M, C, max_active_clusters(bn_stats_kernel<float>));
     if ((size_t)g.gx * g.gy * kCV * Vec<float>::N > (size_t)kMaxPartials) return B200DP_ETOOBIG;
     bn_stats_kernel<float><<<dim3(g.gx, g.gy), kT, 0, s>>>(static_cast<const float*>(x), M, C,
                                                            scratch, stats_local, P, 0);
@@ -714,7 +1047,7 @@ template <typename T>
 int launch_fwd_apply(const FwdArgs& A, bool relu, const b200dp_peers& P, uint32_t seq,
                      cudaStream_t s) {
   const bool res = A.res != nullptr;
-  const Grid2 g = plan_grid<T>(A.M, A.C, res ? kOccBwd : kOccFwd);
+  const Grid2 g = plan_grid<T>(A.M, A.C, kOccFwd);
   const dim3 grid(g.gx, g.gy);
   if (relu && res) bn_fwd_apply_kernel<T, true, true><<<grid, kT, 0, s>>>(A, P, seq);
   else if (relu) bn_fwd_apply_kernel<T, true, false><<<grid, kT, 0, s>>>(A, P, seq);
@@ -770,7 +1103,10 @@ int launch_bwd_reduce(const void* dy, const void* x, const void* yo, int64_t M, 
                       const float* bias, int relu, void* scratch, float* sums_local,
                       float* grad_weight, float* grad_bias, const b200dp_peers& P, uint32_t seq,
                       cudaStream_t s) {
-  const Grid2 g = plan_grid<T>(M, C, kOccBwd);
+  const int maxc = relu == 0   ? max_active_clusters(bn_bwd_reduce_kernel<T, 0>)
+                   : relu == 1 ? max_active_clusters(bn_bwd_reduce_kernel<T, 1>)
+                               : max_active_clusters(bn_bwd_reduce_kernel<T, 2>);
+  const Grid2 g = plan_grid_clustered<T>(M, C, maxc);
   const dim3 grid(g.gx, g.gy);
   const T* pdy = static_cast<const T*>(dy);
   const T* px = static_cast<const T*>(x);

@@ -100,6 +100,40 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
+// ---- sm_100 mixed-precision FP32 arithmetic on bf16 operands ----------------
+// `add/fma.rn.f32.bf16` take bf16 sources straight from a register half (SASS FHADD.BF16 /
+// FHFMA.BF16 with .H0/.H1 selectors) and accumulate in fp32: no unpack instruction, exact
+// products.  They halve the instruction count of the bf16 reduction kernels, which are
+// otherwise issue-bound before they are HBM-bound.
+__device__ __forceinline__ float add_bf16_f32(uint16_t a, float c) {  // float(a) + c
+  float d;
+  asm("add.rn.f32.bf16 %0, %1, %2;" : "=f"(d) : "h"(a), "f"(c));
+  return d;
+}
+__device__ __forceinline__ float fma_bf16_f32(uint16_t a, uint16_t b, float c) {  // float(a)*float(b) + c
+  float d;
+  asm("fma.rn.f32.bf16 %0, %1, %2, %3;" : "=f"(d) : "h"(a), "h"(b), "f"(c));
+  return d;
+}
+__device__ __forceinline__ uint16_t half_lo(uint32_t w) { return (uint16_t)(w & 0xffffu); }
+__device__ __forceinline__ uint16_t half_hi(uint32_t w) { return (uint16_t)(w >> 16); }
+// 16-bit half j (0..7) of a 16-byte vector
+__device__ __forceinline__ uint16_t vec_half(const uint4& v, int j) {
+  const uint32_t w = (j >> 1) == 0 ? v.x : (j >> 1) == 1 ? v.y : (j >> 1) == 2 ? v.z : v.w;
+  return (j & 1) ? half_hi(w) : half_lo(w);
+}
+// packed bf16x2: (a > 0) ? 1.0 : 0.0 per half, and a * b per half (both exact)
+__device__ __forceinline__ uint32_t bf16x2_gt0_mask(uint32_t a) {
+  uint32_t d;
+  asm("set.gt.bf16x2.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(0u));
+  return d;
+}
+__device__ __forceinline__ uint32_t bf16x2_mul(uint32_t a, uint32_t b) {
+  uint32_t d;
+  asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+  return d;
+}
+
 // A 16-byte vector of T seen as floats: 4 (fp32) or 8 (bf16) lanes.
 template <typename T>
 struct Vec;
