@@ -309,14 +309,16 @@ class B200DDP(DistributedDataParallel):
         with torch.cuda.stream(self._comm_stream):
             stream = self._comm_stream.cuda_stream
             n = 0
+            keep_alive = []  # converted copies must outlive the pack launch below
             for k in range(b.p0, b.p1):
                 p = a.params[k]
                 g = p.grad
                 if g is None:
                     a.grad_views[k].zero_()
                     continue
-                if g.dtype != a.dtype or (g.stride() != p.stride() and p.numel() > 1):
+                if g.dtype != a.dtype or not _same_layout(g, p):
                     g = torch.empty_like(p).copy_(g)  # rare: layout or dtype differs from the parameter's
+                    keep_alive.append(g)
                 g.record_stream(self._comm_stream)
                 b.srcs[n] = g.data_ptr()
                 b.numels[n] = p.numel()
@@ -460,6 +462,12 @@ class B200DDP(DistributedDataParallel):
 
     def _get_ddp_logging_data(self):
         return {"backend_name": "b200dp-nvlink-p2p", "world_size": self.world, "rank": self.rank}
+
+
+def _same_layout(g: torch.Tensor, p: torch.Tensor) -> bool:
+    """Same physical element order: strides agree on every dimension longer than 1
+    (a 1x1 conv weight is the same memory whether it is called channels_last or not)."""
+    return all(sg == sp for sg, sp, n in zip(g.stride(), p.stride(), p.shape) if n > 1)
 
 
 def _strided_like(flat: torch.Tensor, p: torch.Tensor) -> torch.Tensor:

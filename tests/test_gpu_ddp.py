@@ -122,6 +122,20 @@ def test_bf16_model_with_syncbn_fusion_trains():
     torch.testing.assert_close(m.bn1.running_mean, ref.bn1.running_mean, rtol=5e-2, atol=2e-2)
 
 
+def test_per_tensor_grads_with_channels_last_input():
+    """Every parameter's gradient, SyncBN-converted + fused + wrapped, against plain torch on the same
+    weights and batch.  (1x1 conv weight gradients arrive with channels_last strides: the pack must
+    treat them as the same memory and must keep converted copies alive until it has run.)"""
+    ref, m = make_pair()
+    ddp = b200.B200DDP(b200.fuse_bn_relu(b200.convert_sync_batchnorm(m)), device_ids=[0])
+    x, y = batch(0, 64)
+    F.cross_entropy(ref(x), y).backward()
+    F.cross_entropy(ddp(x.contiguous(memory_format=torch.channels_last)), y).backward()
+    for (n, a), b in zip(ref.named_parameters(), m.parameters()):
+        err = float((b.grad - a.grad).norm() / (a.grad.norm() + 1e-20))
+        assert err < 2e-2, (n, err)
+
+
 def test_comm_hook_compat():
     _, m = make_pair()
     ddp = b200.B200DDP(m, device_ids=[0])
