@@ -9,10 +9,18 @@
 //     same two IEEE fp32 operations torchvision performs and replicated 32x in
 //     shared memory, one copy per bank, which makes every lookup conflict-free
 //     whatever the pixel values are;
-//   * every thread produces 8 consecutive bf16 outputs and stores them with one
-//     128-bit store.  Crop offset, flip and zero padding are index arithmetic
-//     on the staged bytes.
+//   * every thread produces 8 pixels (24 bf16 outputs, three 128-bit stores); crop
+//     offset, flip and zero padding are index arithmetic on the staged bytes, with
+//     everything per-element folded to compile-time constants.
+// When the host finds that one fp32 FMA per element reproduces the table bit for bit (it
+// does for the usual ImageNet / CIFAR statistics), a table-free variant of the kernel runs
+// instead (see "arithmetic fast path" below).
 // Algorithmic traffic: 1 B read + 2 B written per output element.
+#include <math.h>
+#include <stdlib.h>
+#include <mutex>
+#include <string.h>
+
 #include "common.cuh"
 
 namespace {
@@ -32,7 +40,7 @@ struct AugArgs {
   int rows_per_tile;      // R
   int tiles_per_img;      // ceil(H / R)
   int pitch;              // bytes per staged row (multiple of 16)
-  int chunks_per_row;     // W*3/8 (vector path) or W*3 (scalar path)
+  int chunks_per_row;     // W/8 pixel groups (fast path) or W*3 elements (scalar path)
   uint32_t cpr_magic;     // floor(2^32 / chunks_per_row) + 1
   long long src_bytes;    // B*Hs*Ws*3
   float mean[3], std[3];
@@ -47,6 +55,11 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() {
   asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+// idx / chunks_per_row with the precomputed reciprocal (exact for idx < 2^20)
+__device__ __forceinline__ int row_of(const AugArgs& a, int idx) {
+  return a.chunks_per_row == 1 ? idx : (int)__umulhi((uint32_t)idx, a.cpr_magic);
 }
 
 struct TileInfo {
@@ -70,13 +83,14 @@ __device__ __forceinline__ TileInfo tile_info(const AugArgs& a, int tile) {
 // Stage the source bytes of one tile.  rowshift[r] = offset to add to a byte
 // index inside the SOURCE ROW (column*3 + channel) to get the byte's offset in
 // the staged row, or INT_MIN when the whole row is padding.
+template <int NT>
 __device__ __forceinline__ void stage_tile(const AugArgs& a, const TileInfo& t, uint8_t* buf,
                                            int* rowshift) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int sx0 = t.j - a.pad;
   const int lo = max(sx0, 0) * 3;
   const int hi = min(sx0 + a.W, a.Ws) * 3;
-  for (int r = warp; r < t.rows; r += kThreads / 32) {
+  for (int r = warp; r < t.rows; r += NT / 32) {
     const int sy = t.i + t.y0 + r - a.pad;
     const bool valid = (sy >= 0) && (sy < a.Hs) && (hi > lo);
     if (!valid) {
@@ -97,53 +111,48 @@ __device__ __forceinline__ void stage_tile(const AugArgs& a, const TileInfo& t, 
   }
 }
 
-template <bool PAD>
-__device__ __forceinline__ void emit_tile_vec8(const AugArgs& a, const TileInfo& t,
-                                               const uint8_t* buf, const int* rowshift,
-                                               const float* lut_lane) {
-  const int cpr = a.chunks_per_row;
-  const int nchunks = t.rows * cpr;
+// Fast path (W % 8 == 0): a thread produces 8 whole pixels = 24 outputs = three 128-bit
+// stores.  Starting every thread on a pixel boundary makes the (pixel, channel) of each of
+// its 24 elements a compile-time constant, and the flip a compile-time sign, so the inner
+// loop is one byte load with an immediate offset, one address add and one table load per
+// element (the first version decoded pixel/channel per element with integer arithmetic and
+// was issue-bound at 25 instructions per element).
+template <bool PAD, bool FLIP>
+__device__ __forceinline__ void emit_tile_px8(const AugArgs& a, const TileInfo& t,
+                                              const uint8_t* buf, const int* rowshift,
+                                              const float* lut_lane) {
+  const int gpr = a.chunks_per_row;  // groups of 8 pixels per row
+  const int ngroups = t.rows * gpr;
   const int sx0 = t.j - a.pad;
   uint16_t* out_img = a.dst + ((long long)t.b * a.H + t.y0) * (long long)a.W * 3;
-  for (int idx = threadIdx.x; idx < nchunks; idx += kThreads) {
-    const int r = (int)__umulhi((uint32_t)idx, a.cpr_magic);
-    const int cc = idx - r * cpr;
-    const int e0 = cc * 8;
-    const int x0 = e0 / 3;
-    const int c0 = e0 - 3 * x0;
+  for (int idx = threadIdx.x; idx < ngroups; idx += kThreads) {
+    const int r = row_of(a, idx);
+    const int x0 = (idx - r * gpr) * 8;
     const int shift = rowshift[r];
     const bool rowok = (shift != INT_MIN);
-    // source pixel of output pixel x0, and the per-pixel step
-    const int sxs = sx0 + (t.flip ? (a.W - 1 - x0) : x0);
-    const int step = t.flip ? -1 : 1;
-    const uint8_t* rowp = buf + r * a.pitch + (rowok ? shift : 0);
-    // LUT bases of the three channels in the order this chunk meets them
-    const float* lp[3];
+    const int sxs = sx0 + (FLIP ? (a.W - 1 - x0) : x0);  // source pixel of output pixel x0
+    const uint8_t* base = buf + r * a.pitch + (rowok ? shift : 0) + sxs * 3;
+    float f[24];
 #pragma unroll
-    for (int q = 0; q < 3; ++q) {
-      int c = c0 + q;
-      c = c >= 3 ? c - 3 : c;
-      lp[q] = lut_lane + c * (256 * 32);
-    }
-    float f[8];
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const int pos = c0 + k;                 // 0..9
-      const int dxp = (pos * 11) >> 5;        // pos / 3 for pos < 32
-      const int c = pos - 3 * dxp;            // absolute channel is (c0+k)%3 == c
-      const int sx = sxs + step * dxp;
-      int v;
+    for (int p = 0; p < 8; ++p) {
+      bool ok = true;
       if (PAD) {
-        const bool ok = rowok && (sx >= 0) && (sx < a.Ws);
-        v = ok ? (int)rowp[sx * 3 + c] : 0;
-      } else {
-        v = (int)rowp[sx * 3 + c];
+        const int sx = FLIP ? sxs - p : sxs + p;
+        ok = rowok && (sx >= 0) && (sx < a.Ws);
       }
-      f[k] = lp[k % 3][v * 32];
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const int off = (FLIP ? -3 * p : 3 * p) + c;  // constant after unrolling
+        int v = 0;
+        if (!PAD || ok) v = base[off];
+        f[3 * p + c] = lut_lane[c * (256 * 32) + v * 32];
+      }
     }
-    uint4 o = make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]),
-                         pack_bf16(f[6], f[7]));
-    st_stream(out_img + (long long)r * a.W * 3 + e0, o);
+    uint16_t* o = out_img + ((long long)r * a.W + x0) * 3;
+#pragma unroll
+    for (int q = 0; q < 3; ++q)
+      st_stream(o + 8 * q, make_uint4(pack_bf16(f[8 * q + 0], f[8 * q + 1]), pack_bf16(f[8 * q + 2], f[8 * q + 3]),
+                                      pack_bf16(f[8 * q + 4], f[8 * q + 5]), pack_bf16(f[8 * q + 6], f[8 * q + 7])));
   }
 }
 
@@ -157,7 +166,7 @@ __device__ __forceinline__ void emit_tile_scalar(const AugArgs& a, const TileInf
   const int sx0 = t.j - a.pad;
   uint16_t* out_img = a.dst + ((long long)t.b * a.H + t.y0) * (long long)a.W * 3;
   for (int idx = threadIdx.x; idx < n; idx += kThreads) {
-    const int r = (int)__umulhi((uint32_t)idx, a.cpr_magic);
+    const int r = row_of(a, idx);
     const int e = idx - r * epr;
     const int x = e / 3, c = e - 3 * x;
     const int shift = rowshift[r];
@@ -180,7 +189,7 @@ __global__ void __launch_bounds__(kThreads, 1) augment_kernel(const AugArgs a, i
   int tile = blockIdx.x;
   if (tile >= total_tiles) return;
   TileInfo cur = tile_info(a, tile);
-  stage_tile(a, cur, tilebuf, rowshift);
+  stage_tile<kThreads>(a, cur, tilebuf, rowshift);
   cp_async_commit();
 
   // Build the table while the first loads are in flight: torchvision's
@@ -200,16 +209,19 @@ __global__ void __launch_bounds__(kThreads, 1) augment_kernel(const AugArgs a, i
     TileInfo nxt;
     if (next < total_tiles) {
       nxt = tile_info(a, next);
-      stage_tile(a, nxt, tilebuf + (p ^ 1) * kTileBytes, rowshift + (p ^ 1) * kMaxRows);
+      stage_tile<kThreads>(a, nxt, tilebuf + (p ^ 1) * kTileBytes, rowshift + (p ^ 1) * kMaxRows);
       cp_async_commit();
       cp_async_wait<1>();
     } else {
       cp_async_wait<0>();
     }
     __syncthreads();  // staged bytes, rowshift (and, first time round, the LUT) visible
-    if (VEC8)
-      emit_tile_vec8<PAD>(a, cur, tilebuf + p * kTileBytes, rowshift + p * kMaxRows, lut_lane);
-    else
+    if (VEC8) {
+      if (cur.flip)
+        emit_tile_px8<PAD, true>(a, cur, tilebuf + p * kTileBytes, rowshift + p * kMaxRows, lut_lane);
+      else
+        emit_tile_px8<PAD, false>(a, cur, tilebuf + p * kTileBytes, rowshift + p * kMaxRows, lut_lane);
+    } else
       emit_tile_scalar<PAD>(a, cur, tilebuf + p * kTileBytes, rowshift + p * kMaxRows, lut_lane);
     if (next >= total_tiles) break;
     __syncthreads();  // everyone is done with buffer p before it is refilled
@@ -217,6 +229,174 @@ __global__ void __launch_bounds__(kThreads, 1) augment_kernel(const AugArgs a, i
     cur = nxt;
     p ^= 1;
   }
+}
+
+// ---- arithmetic fast path ---------------------------------------------------------
+// When the host has checked, for all 3*256 inputs, that bf16(fma(v, A[c], B[c])) equals the
+// bf16 rounding of torchvision's two-step result, the table is not needed: the kernel
+// converts and applies one FMA per element.  That removes one shared-memory load per element
+// (the table version is bound by the shared-memory instruction queue, not by HBM), frees
+// 96 KB of shared memory and lets three CTAs share an SM.  The staged bytes of a group of 8
+// pixels are fetched as 7 aligned words and realigned with funnel shifts.
+constexpr int kAffThreads = 512;
+constexpr int kAffTileBytes = 25 * 1024;
+constexpr int kAffSlack = 64;  // bytes in front of the buffers: left padding may index before a row
+
+struct AffineCoef {
+  float A[3], B[3];
+};
+
+template <bool PAD, bool FLIP>
+__device__ __forceinline__ void emit_tile_affine(const AugArgs& a, const AffineCoef& k, const TileInfo& t,
+                                                 const uint8_t* buf, const int* rowshift) {
+  const int gpr = a.chunks_per_row;  // groups of 8 pixels per row
+  const int ngroups = t.rows * gpr;
+  const int sx0 = t.j - a.pad;
+  uint16_t* out_img = a.dst + ((long long)t.b * a.H + t.y0) * (long long)a.W * 3;
+  for (int idx = threadIdx.x; idx < ngroups; idx += kAffThreads) {
+    const int r = row_of(a, idx);
+    const int x0 = (idx - r * gpr) * 8;
+    const int shift = rowshift[r];
+    const bool rowok = (shift != INT_MIN);
+    // lowest source pixel of the group; output pixel p reads block pixel p (or 7-p when flipped)
+    const int sxlo = sx0 + (FLIP ? (a.W - 8 - x0) : x0);
+    uint32_t u[6] = {0, 0, 0, 0, 0, 0};
+    if (!PAD || rowok) {
+      const uint8_t* blk = buf + r * a.pitch + shift + sxlo * 3;
+      const uint32_t addr = (uint32_t)__cvta_generic_to_shared(blk);
+      const uint32_t al = addr & ~3u, sh = (addr & 3u) * 8;
+      uint32_t w[7];
+#pragma unroll
+      for (int i = 0; i < 7; ++i) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w[i]) : "r"(al + 4 * i));
+#pragma unroll
+      for (int i = 0; i < 6; ++i) u[i] = __funnelshift_r(w[i], w[i + 1], sh);
+    }
+    uint32_t o[12];
+#pragma unroll
+    for (int p = 0; p < 8; ++p) {
+      const int bp = FLIP ? 7 - p : p;  // pixel inside the 24-byte block
+      bool ok = true;
+      if (PAD) {
+        const int sx = sxlo + bp;
+        ok = rowok && (sx >= 0) && (sx < a.Ws);
+      }
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const int b = 3 * bp + c;  // byte index in the block: constant after unrolling
+        uint32_t v = (u[b >> 2] >> (8 * (b & 3))) & 0xffu;
+        if (PAD) v = ok ? v : 0u;
+        const float f = fmaf((float)v, k.A[c], k.B[c]);
+        const int e = 3 * p + c;
+        if (e & 1) o[e >> 1] = pack_bf16(__uint_as_float(o[e >> 1]), f);
+        else o[e >> 1] = __float_as_uint(f);
+      }
+    }
+    uint16_t* dst = out_img + ((long long)r * a.W + x0) * 3;
+#pragma unroll
+    for (int q = 0; q < 3; ++q) st_stream(dst + 8 * q, make_uint4(o[4 * q], o[4 * q + 1], o[4 * q + 2], o[4 * q + 3]));
+  }
+}
+
+template <bool PAD>
+__global__ void __launch_bounds__(kAffThreads, 3) augment_affine_kernel(const AugArgs a, const AffineCoef k,
+                                                                        int total_tiles) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  uint8_t* tilebuf = smem + kAffSlack;                                           // [2][kAffTileBytes]
+  int* rowshift = reinterpret_cast<int*>(smem + kAffSlack + 2 * kAffTileBytes + 16);  // [2][kMaxRows]
+  int tile = blockIdx.x;
+  if (tile >= total_tiles) return;
+  TileInfo cur = tile_info(a, tile);
+  stage_tile<kAffThreads>(a, cur, tilebuf, rowshift);
+  cp_async_commit();
+  int p = 0;
+  while (true) {
+    const int next = tile + gridDim.x;
+    TileInfo nxt;
+    if (next < total_tiles) {
+      nxt = tile_info(a, next);
+      stage_tile<kAffThreads>(a, nxt, tilebuf + (p ^ 1) * kAffTileBytes, rowshift + (p ^ 1) * kMaxRows);
+      cp_async_commit();
+      cp_async_wait<1>();
+    } else {
+      cp_async_wait<0>();
+    }
+    __syncthreads();
+    if (cur.flip) emit_tile_affine<PAD, true>(a, k, cur, tilebuf + p * kAffTileBytes, rowshift + p * kMaxRows);
+    else emit_tile_affine<PAD, false>(a, k, cur, tilebuf + p * kAffTileBytes, rowshift + p * kMaxRows);
+    if (next >= total_tiles) break;
+    __syncthreads();
+    tile = next;
+    cur = nxt;
+    p ^= 1;
+  }
+}
+
+constexpr size_t kAffSmemBytes = kAffSlack + 2 * kAffTileBytes + 16 + 2 * kMaxRows * sizeof(int);
+
+// bf16 bits of an fp32 value, round to nearest even (finite inputs)
+inline uint16_t host_bf16(float f) {
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  return (uint16_t)((u + 0x7fffu + ((u >> 16) & 1u)) >> 16);
+}
+
+// Is bf16(fma(v, A, B)) == bf16(((v / 255) - mean) / std) for every byte value v and channel?
+// 768 evaluations on the host per new (mean, std); the answer is cached.
+bool affine_is_exact(const float* mean, const float* std, AffineCoef* k) {
+  static float cm[3], cs[3];
+  static AffineCoef ck;
+  static int cached = 0;  // 0 unknown, 1 exact, 2 not exact
+  static std::mutex mu;
+  std::lock_guard<std::mutex> lock(mu);
+  if (cached && !memcmp(cm, mean, 12) && !memcmp(cs, std, 12)) {
+    *k = ck;
+    return cached == 1;
+  }
+  bool exact = true;
+  for (int c = 0; c < 3; ++c) {
+    ck.A[c] = (float)(1.0 / (255.0 * (double)std[c]));
+    ck.B[c] = (float)(-(double)mean[c] / (double)std[c]);
+    for (int v = 0; v < 256 && exact; ++v) {
+      volatile float x = (float)v / 255.0f;  // volatile: keep every step rounded to fp32
+      volatile float t = x - mean[c];
+      volatile float want = t / std[c];
+      const float got = fmaf((float)v, ck.A[c], ck.B[c]);
+      exact = host_bf16(want) == host_bf16(got);
+    }
+  }
+  memcpy(cm, mean, 12);
+  memcpy(cs, std, 12);
+  cached = exact ? 1 : 2;
+  *k = ck;
+  return exact;
+}
+
+template <bool PAD>
+int launch_affine(const AugArgs& a, const AffineCoef& k, int total_tiles, cudaStream_t s) {
+  B200DP_CUDA_TRY(cudaFuncSetAttribute(augment_affine_kernel<PAD>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)kAffSmemBytes));
+  const int cap = 3 * B200DP_NUM_SMS;
+  const int grid = total_tiles < cap ? total_tiles : cap;
+  augment_affine_kernel<PAD><<<grid, kAffThreads, kAffSmemBytes, s>>>(a, k, total_tiles);
+  B200DP_LAUNCH_CHECK();
+  return B200DP_OK;
+}
+
+// rows per tile: as many as fit, but preferring a count whose pixel groups fill whole rounds of
+// the CTA's threads (a round that is 5 % full costs as much as a full one)
+int pick_rows(int H, int rmax, int groups_per_row, int threads) {
+  if (rmax > H) rmax = H;
+  int best = rmax;
+  double best_eff = 0.0;
+  for (int r = rmax; r >= (rmax + 1) / 2 && r >= 1; --r) {
+    const int g = r * groups_per_row;
+    const double eff = (double)g / (double)(((g + threads - 1) / threads) * threads);
+    if (eff > best_eff + 0.02) {
+      best_eff = eff;
+      best = r;
+    }
+  }
+  return best;
 }
 
 constexpr size_t kSmemBytes =
@@ -256,18 +436,32 @@ extern "C" int b200dp_augment_u8_bf16(const uint8_t* src, int B, int Hs, int Ws,
   for (int c = 0; c < 3; ++c) { a.mean[c] = mean[c]; a.std[c] = std[c]; }
   // a staged row holds at most the W*3 needed bytes plus 15 of alignment slack
   a.pitch = ((W * 3 + 15 + 15) / 16) * 16;
-  if (a.pitch > kTileBytes) return B200DP_EUNSUPPORTED;  // rows wider than ~4000 pixels
+  const bool vec8 = (W % 8) == 0;
+  a.chunks_per_row = vec8 ? W / 8 : W * 3;  // groups of 8 pixels, or single elements
+  a.cpr_magic = (uint32_t)(0x100000000ULL / (unsigned)a.chunks_per_row) + 1u;
+  cudaStream_t s = (cudaStream_t)stream;
+  AffineCoef k;
+  // B200DP_AUGMENT_FORCE_TABLE=1 keeps the table kernel reachable for tests
+  const char* force_table = getenv("B200DP_AUGMENT_FORCE_TABLE");
+  const bool table_only = force_table && force_table[0] == '1';
+  if (!table_only && vec8 && a.pitch <= kAffTileBytes && pad * 3 + 4 <= kAffSlack &&
+      affine_is_exact(mean, std, &k)) {
+    int rmax = kAffTileBytes / a.pitch;
+    if (rmax > kMaxRows) rmax = kMaxRows;
+    a.rows_per_tile = pick_rows(H, rmax, a.chunks_per_row, kAffThreads);
+    a.tiles_per_img = (H + a.rows_per_tile - 1) / a.rows_per_tile;
+    const long long total = (long long)B * a.tiles_per_img;
+    if (total > 0x7fffffffLL) return B200DP_ETOOBIG;
+    return pad ? launch_affine<true>(a, k, (int)total, s) : launch_affine<false>(a, k, (int)total, s);
+  }
+  if (a.pitch > kTileBytes) return B200DP_EUNSUPPORTED;  // rows wider than ~16000 pixels
   int R = kTileBytes / a.pitch;
   if (R > kMaxRows) R = kMaxRows;
   if (R > H) R = H;
   a.tiles_per_img = (H + R - 1) / R;
   a.rows_per_tile = (H + a.tiles_per_img - 1) / a.tiles_per_img;  // equal-sized tiles
-  const bool vec8 = ((W * 3) % 8) == 0;
-  a.chunks_per_row = vec8 ? (W * 3) / 8 : W * 3;
-  a.cpr_magic = (uint32_t)(0x100000000ULL / (unsigned)a.chunks_per_row) + 1u;
   const long long total = (long long)B * a.tiles_per_img;
   if (total > 0x7fffffffLL) return B200DP_ETOOBIG;
-  cudaStream_t s = (cudaStream_t)stream;
   if (vec8) return pad ? launch<true, true>(a, (int)total, s) : launch<true, false>(a, (int)total, s);
   return pad ? launch<false, true>(a, (int)total, s) : launch<false, false>(a, (int)total, s);
 }

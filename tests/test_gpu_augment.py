@@ -44,6 +44,30 @@ def test_against_oracle(B, src, out, pad):
     assert np.array_equal(bits(got), transform_ref.f32_to_bf16_bits(want))
 
 
+def test_table_kernel_matches_arithmetic_kernel(monkeypatch):
+    """The library picks a table-free kernel when one FMA per element reproduces the table exactly;
+    the table kernel (any mean/std) must give the same bits."""
+    x = torch.randint(0, 256, (9, 40, 48, 3), dtype=torch.uint8)
+    for pad, out in ((0, 32), (4, 40)):
+        params = T.draw_crop_flip_params(9, (40, 48), (out, out), pad, generator=torch.Generator().manual_seed(pad))
+        tf = b200.BatchTransform(out, padding=pad)
+        fast = tf(x.cuda(), params=params)
+        monkeypatch.setenv("B200DP_AUGMENT_FORCE_TABLE", "1")
+        table = tf(x.cuda(), params=params)
+        monkeypatch.delenv("B200DP_AUGMENT_FORCE_TABLE")
+        want = transform_ref.crop_flip_normalize(x.numpy(), params.numpy(), pad, (out, out),
+                                                 np.float32(T.IMAGENET_MEAN), np.float32(T.IMAGENET_STD))
+        assert np.array_equal(bits(table), transform_ref.f32_to_bf16_bits(want))
+        assert torch.equal(fast, table)
+    # statistics for which no single FMA reproduces the two-step rounding fall back to the table
+    odd = b200.BatchTransform(32, mean=(0.3337, 0.1, 0.7777), std=(0.0123, 3.3, 0.9))
+    p = T.draw_crop_flip_params(9, (40, 48), (32, 32), 0, generator=torch.Generator().manual_seed(5))
+    got = odd(x.cuda(), params=p)
+    want = transform_ref.crop_flip_normalize(x.numpy(), p.numpy(), 0, (32, 32), np.float32((0.3337, 0.1, 0.7777)),
+                                             np.float32((0.0123, 3.3, 0.9)))
+    assert np.array_equal(bits(got), transform_ref.f32_to_bf16_bits(want))
+
+
 def test_extreme_offsets_and_all_flipped():
     B, src, out, pad = 4, 16, 16, 4
     x = np.random.default_rng(1).integers(0, 256, size=(B, src, src, 3), dtype=np.uint8)
