@@ -67,6 +67,42 @@ def test_draws_match_live_torchvision():
         b200.draw_crop_flip_params(1, (8, 8), (16, 16))
 
 
+def test_bulk_draws_replicate_the_per_sample_loop():
+    from dbx_distributed_pytorch_examples_b200.transform import _draw_crop_flip_params_loop
+    for seed in (0, 7, 2 ** 31 + 11):
+        ga, gb = torch.Generator().manual_seed(seed), torch.Generator().manual_seed(seed)
+        for n, src, out, pad in ((3, 32, 32, 4), (700, 256, 224, 0), (40, 64, 64, 0), (1, 8, 8, 1), (650, 40, 32, 0)):
+            want = _draw_crop_flip_params_loop(n, (src, src + 1), (out, out), pad, generator=ga)
+            got = b200.draw_crop_flip_params(n, (src, src + 1), (out, out), pad, generator=gb)
+            assert torch.equal(got, want)
+        # the generator is left exactly where the loop leaves it
+        assert torch.equal(ga.get_state(), gb.get_state())
+        assert torch.equal(torch.randn(7, generator=ga), torch.randn(7, generator=gb))
+
+
+def test_sharded_batch_sampler_matches_distributed_sampler(golden):
+    from torch.utils.data.distributed import DistributedSampler
+    g = golden("sampler_buckets.npz")
+    for world in (2, 4):
+        for rank in range(world):
+            for epoch in (0, 1):
+                s = b200.ShardedBatchSampler(1003, 64, rank=rank, world=world, seed=0)
+                s.set_epoch(epoch)
+                flat = torch.cat(list(s)).numpy()
+                assert np.array_equal(flat, g[f"w{world}_r{rank}_e{epoch}"])        # golden from torch
+                assert np.array_equal(flat, ddp_ref.distributed_sampler_indices(1003, world, rank, g[f"perm_e{epoch}"]))
+                assert len(s) == len(list(s)) == -(-len(flat) // 64)
+    live = DistributedSampler(list(range(10)), num_replicas=4, rank=3, shuffle=False)
+    ours = b200.ShardedBatchSampler(10, 2, rank=3, world=4, shuffle=False)
+    assert torch.cat(list(ours)).tolist() == list(iter(live))
+    ds = b200.PinnedImageDataset(torch.arange(10 * 2 * 2 * 3, dtype=torch.uint8).view(10, 2, 2, 3), torch.arange(10), pin=False)
+    batches = [(im.clone(), lb.clone()) for im, lb in ds.batches(ours)]
+    assert [lb.tolist() for _, lb in batches] == [[3, 7], [1]]
+    assert torch.equal(batches[0][0][1], ds.images[7])
+    with pytest.raises(ValueError):
+        b200.ShardedBatchSampler(10, 2, rank=4, world=4)
+
+
 def test_bucket_plan_matches_ddp_assignment():
     model = workloads.cifar_resnet18()
     params = list(reversed(list(model.parameters())))
