@@ -204,9 +204,11 @@ class KernelProfiler:
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "torch-gpu"],
+                    help="b200 = this library; reference = the reference stack on host cores; torch-gpu = stock torch "
+                         "BatchNorm/DDP(NCCL)/optim on the same GPUs (context only, not part of the contract)")
     ap.add_argument("--batch", type=int, default=PER_GPU_BATCH, help="per-GPU batch (256 is the named config)")
     ap.add_argument("--optimizer", default="sgd", choices=["sgd", "adam"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -236,14 +238,22 @@ def main():
 
     torch.manual_seed(0)
     model = workloads.resnet50(CLASSES)
-    model = b200.fuse_bn_relu(b200.convert_sync_batchnorm(model)).to(dev)
-    model = model.to(torch.bfloat16).to(memory_format=torch.channels_last)
-    ddp = b200.B200DDP(model, device_ids=[local_rank], output_device=local_rank)
+    stock = args.impl == "torch-gpu"
+    if stock:  # stock torch on the same GPU(s): nn.SyncBatchNorm, DistributedDataParallel over NCCL, torch.optim
+        if world > 1:
+            model = torch.nn.SyncBatchNorm.convert_sync_batchnorm(model)
+        model = model.to(dev).to(torch.bfloat16).to(memory_format=torch.channels_last)
+        ddp = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local_rank]) if world > 1 else model
+    else:
+        model = b200.fuse_bn_relu(b200.convert_sync_batchnorm(model)).to(dev)
+        model = model.to(torch.bfloat16).to(memory_format=torch.channels_last)
+        ddp = b200.B200DDP(model, device_ids=[local_rank], output_device=local_rank)
     if args.optimizer == "sgd":  # 01_basic_torch_distributor.py:294
         opt = torch.optim.SGD(ddp.parameters(), lr=1e-3, momentum=0.5)
     else:                        # 02_cifar_torch_distributor_resnet.py:213
         opt = torch.optim.Adam(ddp.parameters(), lr=1e-3)
-    ddp.fuse_optimizer(opt)
+    if not stock:
+        ddp.fuse_optimizer(opt)
     tf = b200.BatchTransform(OUT_HW, device=dev)
 
     B = args.batch
@@ -302,13 +312,15 @@ def main():
     e2e_losses = []
     ms_e2e = timed(lambda: e2e_losses.extend(e2e_epoch(args.steps)), 1)
     assert len(e2e_losses) == args.steps
-    ddp.comm.check_error()
+    if not stock:
+        ddp.comm.check_error()
 
     images = B * world * args.steps
     value = images / (ms_dev / 1e3)
     e2e = images / (ms_e2e / 1e3)
 
     line = {
+        **({"impl": "torch-gpu"} if stock else {}),
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
@@ -323,7 +335,7 @@ def main():
         "loss": loss_dev,
     }
 
-    if rank == 0 and not args.no_kernel_pass:
+    if rank == 0 and not args.no_kernel_pass and not stock:
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -331,7 +343,7 @@ def main():
             pass
         peak = peaks.get("hbm_gbs", 6650.0)
         line["roofline_peak_source"] = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
-    if not args.no_kernel_pass:
+    if not args.no_kernel_pass and not stock:
         # every rank runs the instrumented steps (they contain collectives); rank 0 reports
         prof = KernelProfiler()
         _lib.PROFILER = prof

@@ -16,7 +16,7 @@ library or without a GPU the entry points raise.
 """
 from ._lib import B200DPError, build  # noqa: F401
 from .comm import Communicator  # noqa: F401
-from .ddp import B200DDP  # noqa: F401
+from .ddp import B200DDP, prepare_model  # noqa: F401
 from .distributor import DeepspeedTorchDistributor, TorchDistributor  # noqa: F401
 from .feed import DeviceFeeder, LossReader, PinnedImageDataset, ShardedBatchSampler  # noqa: F401
 from .fusion import fuse_bn_relu  # noqa: F401
@@ -24,7 +24,7 @@ from .syncbn import B200SyncBatchNorm, convert_sync_batchnorm  # noqa: F401
 from .transform import BatchTransform, draw_crop_flip_params  # noqa: F401
 
 __all__ = [
-    "B200DDP", "B200SyncBatchNorm", "BatchTransform", "Communicator", "TorchDistributor",
+    "B200DDP", "prepare_model", "B200SyncBatchNorm", "BatchTransform", "Communicator", "TorchDistributor",
     "DeepspeedTorchDistributor", "convert_sync_batchnorm", "fuse_bn_relu", "draw_crop_flip_params",
     "B200DPError", "build", "DeviceFeeder", "LossReader", "PinnedImageDataset", "ShardedBatchSampler",
 ]

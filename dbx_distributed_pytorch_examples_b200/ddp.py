@@ -266,6 +266,7 @@ class B200DDP(DistributedDataParallel):
         self._seqs = [self.comm.next_seq() for _ in self._buckets]
         if self._optimizer is not None:
             self._opt_step_count += 1
+            self._state_stale = True
 
     @contextmanager
     def no_sync(self):
@@ -418,6 +419,8 @@ class B200DDP(DistributedDataParallel):
                     st["exp_avg"] = a.state1[off:off + p.numel()].view(p.shape)
                     st["exp_avg_sq"] = a.state2[off:off + p.numel()].view(p.shape)
         ddp = self
+        self._state_stale = False
+        optimizer.register_state_dict_pre_hook(self._check_state_consolidated)
 
         def step(closure=None):
             loss = closure() if closure is not None else None
@@ -453,6 +456,37 @@ class B200DDP(DistributedDataParallel):
             o.bias_correction2_sqrt = math.sqrt(1.0 - b2 ** t)
         return o
 
+    # ---- checkpoint support ----------------------------------------------------------------
+    def consolidate_optimizer_state(self):
+        """Make every rank's fused optimizer state complete.  COLLECTIVE: call it on all ranks
+        (e.g. right before ``if rank == 0: save_checkpoint(...)``,
+        01_torch_distributor/01_basic_torch_distributor.py:239-245,298-299).
+
+        Under the two-shot kernel rank r only maintains the r-th 1/N slice of each bucket's
+        momentum / Adam moments / fp32 master weights; this all-gathers the slices over the
+        process group (epoch-rate, so torch.distributed is fine here), after which
+        ``optimizer.state_dict()`` holds exactly what a replicated torch optimizer would."""
+        if self._optimizer is None or self.world == 1:
+            self._state_stale = False
+            return
+        torch.cuda.current_stream(self.device).wait_stream(self._comm_stream)
+        for b in self._buckets:
+            a = b.arena
+            sl = b.numel // self.world
+            for buf in (a.state1, a.state2, a.master):
+                if buf is None:
+                    continue
+                whole = buf[b.start:b.start + b.numel]
+                mine = whole[self.rank * sl:(self.rank + 1) * sl].clone()
+                dist.all_gather_into_tensor(whole, mine, group=self.process_group)
+        self._state_stale = False
+
+    def _check_state_consolidated(self, *_):
+        if self.world > 1 and getattr(self, "_state_stale", False):
+            raise RuntimeError(
+                "the fused optimizer's state is sharded across ranks (each rank updates 1/N of every bucket): "
+                "call ddp.consolidate_optimizer_state() on ALL ranks before optimizer.state_dict()")
+
     # ---- housekeeping ---------------------------------------------------------------------
     def bucket_sizes_bytes(self):
         return [b.numel * b.arena.esize for b in self._buckets]
@@ -462,6 +496,33 @@ class B200DDP(DistributedDataParallel):
 
     def _get_ddp_logging_data(self):
         return {"backend_name": "b200dp-nvlink-p2p", "world_size": self.world, "rank": self.rank}
+
+
+def prepare_model(model: torch.nn.Module, device=None, *, sync_batchnorm: bool = True, fuse: bool = True,
+                  channels_last: bool = True, dtype: Optional[torch.dtype] = None, **ddp_kwargs) -> "B200DDP":
+    """One call for what Accelerate's ``accelerator.prepare(model)`` (04_accelerate/01_cifar_accelerate.ipynb:503)
+    and Ray's ``ray.train.torch.prepare_model(model)`` (05_ray/02_cifar_resnet_pytorch_ray.ipynb:280) do for the
+    reference — move the model to this rank's GPU and wrap it for data-parallel training — plus the
+    conversions this library adds (SyncBatchNorm replacement, BN+ReLU fusion, channels_last, dtype).
+    The result passes ``isinstance(m, DistributedDataParallel)`` and exposes ``.module`` as both expect."""
+    import os
+
+    from .fusion import fuse_bn_relu
+    from .syncbn import convert_sync_batchnorm
+
+    if device is None:
+        device = torch.device("cuda", int(os.environ.get("LOCAL_RANK", torch.cuda.current_device())))
+    device = torch.device(device)
+    if sync_batchnorm:
+        model = convert_sync_batchnorm(model)
+        if fuse:
+            model = fuse_bn_relu(model)
+    model = model.to(device)
+    if dtype is not None:
+        model = model.to(dtype)
+    if channels_last:
+        model = model.to(memory_format=torch.channels_last)
+    return B200DDP(model, device_ids=[device.index], output_device=device.index, **ddp_kwargs)
 
 
 def _same_layout(g: torch.Tensor, p: torch.Tensor) -> bool:

@@ -219,6 +219,64 @@ def _w_ddp_syncbn_vs_torch():
     return "ok"
 
 
+def _w_checkpoint():
+    """save_checkpoint of the reference (model.module.state_dict() + optimizer.state_dict() on rank 0,
+    01_basic_torch_distributor.py:239-245) with the fused, sharded optimizer: after consolidation the
+    checkpoint equals the one a replicated torch SGD writes."""
+    import copy
+    import io
+    import torch
+    import torch.distributed as dist
+    import torch.nn.functional as F
+    import dbx_distributed_pytorch_examples_b200 as b200
+    from dbx_distributed_pytorch_examples_b200 import workloads
+    rank, world = _init()
+    torch.manual_seed(0)
+    base = workloads.cifar_resnet18(10).cuda()
+    ref = torch.nn.parallel.DistributedDataParallel(copy.deepcopy(base), device_ids=[rank])
+    ours = b200.prepare_model(copy.deepcopy(base), sync_batchnorm=False, channels_last=False)
+    assert isinstance(ours, torch.nn.parallel.DistributedDataParallel) and ours.module is not None
+    o_ref = torch.optim.SGD(ref.parameters(), lr=1e-3, momentum=0.5)
+    o_our = ours.fuse_optimizer(torch.optim.SGD(ours.parameters(), lr=1e-3, momentum=0.5))
+    for step in range(3):
+        gen = torch.Generator().manual_seed(50 * rank + step)
+        x, y = torch.randn(32, 3, 32, 32, generator=gen).cuda(), torch.randint(0, 10, (32,), generator=gen).cuda()
+        for m, o in ((ref, o_ref), (ours, o_our)):
+            o.zero_grad(); F.cross_entropy(m(x), y).backward(); o.step()
+    try:
+        o_our.state_dict()
+        raise AssertionError("state_dict() of a sharded state must ask for consolidation")
+    except RuntimeError as e:
+        assert "consolidate_optimizer_state" in str(e)
+    ours.consolidate_optimizer_state()          # collective, all ranks
+    if rank == 0:                               # the reference's save_checkpoint, rank 0 only
+        blob = io.BytesIO()
+        torch.save({"model": ours.module.state_dict(), "optimizer": o_our.state_dict()}, blob)
+        assert blob.tell() < 3 * 45e6, "checkpoint must not drag the whole symmetric heap along"
+        blob.seek(0)
+        ck = torch.load(blob)
+        want_m, want_o = ref.module.state_dict(), o_ref.state_dict()
+        assert list(ck["model"]) == list(want_m)
+        for k in want_m:
+            torch.testing.assert_close(ck["model"][k], want_m[k], rtol=1e-5, atol=1e-6)
+        assert ck["optimizer"]["param_groups"][0]["momentum"] == 0.5
+        for idx, st in want_o["state"].items():
+            torch.testing.assert_close(ck["optimizer"]["state"][idx]["momentum_buffer"], st["momentum_buffer"],
+                                       rtol=1e-5, atol=1e-7)
+        # and it loads back into a plain torch model + optimizer (resume path)
+        plain = copy.deepcopy(base)
+        plain.load_state_dict(ck["model"])
+        po = torch.optim.SGD(plain.parameters(), lr=1e-3, momentum=0.5)
+        po.load_state_dict(ck["optimizer"])
+    dist.barrier()
+    dist.destroy_process_group()
+    return "ok"
+
+
+def test_checkpoint_round_trip_two_ranks():
+    assert TorchDistributor(num_processes=2).run(_w_checkpoint) == "ok"
+
+
 def test_syncbn_two_ranks():
     assert TorchDistributor(num_processes=2).run(_w_syncbn) == "ok"
 
