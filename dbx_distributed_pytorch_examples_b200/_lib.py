@@ -75,7 +75,7 @@ CALLS = {}
 PROFILER = None
 _COMPUTE = ("b200dp_augment_u8_bf16", "b200dp_bn_fwd_stats", "b200dp_bn_fwd_stats_noalloc", "b200dp_bn_fwd_apply", "b200dp_bn_inference",
             "b200dp_bn_bwd_reduce", "b200dp_bn_bwd_apply", "b200dp_bucket_pack", "b200dp_allreduce_update",
-            "b200dp_comm_barrier")
+            "b200dp_comm_barrier", "b200dp_bn_forward", "b200dp_bn_backward")
 
 
 class _Entry:
@@ -118,6 +118,10 @@ _SIGNATURES = {
                                      c_int, _VP, _VP, _VP, _VP, _VP, c_uint32, _VP]),
     "b200dp_bn_bwd_apply": (c_int, [_VP, _VP, _VP, _VP, _VP, c_int, c_int64, c_int, _VP, _VP, _VP,
                                     _VP, _VP, _VP, c_int, _VP, c_uint32, _VP]),
+    "b200dp_bn_forward": (c_int, [_VP, _VP, _VP, c_int, c_int64, c_int, _VP, _VP, _VP, _VP, c_float, c_float,
+                                  _VP, _VP, _VP, c_int, _VP, c_uint32, _VP]),
+    "b200dp_bn_backward": (c_int, [_VP, _VP, _VP, _VP, _VP, c_int, c_int64, c_int, _VP, _VP, _VP, c_int, _VP, _VP,
+                                   _VP, _VP, _VP, c_uint32, _VP]),
     "b200dp_comm_create": (c_int, [c_int, c_int, c_size_t, POINTER(_VP)]),
     "b200dp_comm_export": (c_int, [_VP, _VP]),
     "b200dp_comm_open_peers": (c_int, [_VP, _VP]),
@@ -187,3 +191,15 @@ def current_stream() -> int:
     import torch
 
     return torch.cuda.current_stream().cuda_stream
+
+
+def raw_stream(device_index: int) -> int:
+    """cudaStream_t of torch's current stream on that device, without building a Stream object
+    (torch.cuda.current_stream() costs ~10 us per call; this is the call TorchInductor uses)."""
+    import torch
+
+    return torch._C._cuda_getCurrentRawStream(device_index)
+
+
+# launches of bn_forward / bn_backward are two kernels each: bench.py counts kernels, not calls
+LAUNCHES_PER_CALL = {"b200dp_bn_forward": 2, "b200dp_bn_backward": 2}

@@ -1186,3 +1186,33 @@ extern "C" int b200dp_bn_bwd_apply(const void* dy, const void* x, const void* y_
   return dtype == B200DP_BF16 ? launch_bwd_apply<__nv_bfloat16>(A, relu, P, seq, s)
                               : launch_bwd_apply<float>(A, relu, P, seq, s);
 }
+
+// ---- one call per direction -------------------------------------------------------
+// The Python host pays several microseconds per foreign call; for the small layers of
+// CIFAR / 64x64 models that is as long as the kernels themselves.  These two entry points
+// issue the same two launches as the four above with a single crossing of the boundary.
+extern "C" int b200dp_bn_forward(const void* x, const void* residual, void* y, int dtype, int64_t M,
+                                 int C, void* scratch, float* stats_local, const float* weight,
+                                 const float* bias, float eps, float momentum, float* running_mean,
+                                 float* running_var, float* save, int relu, b200dp_comm* comm,
+                                 uint32_t seq, b200dp_stream_t stream) {
+  if (!save) return B200DP_EINVAL;
+  int rc = b200dp_bn_fwd_stats(x, dtype, M, C, scratch, stats_local, comm, seq, stream);
+  if (rc) return rc;
+  return b200dp_bn_fwd_apply(x, residual, y, dtype, M, C, stats_local, weight, bias, eps, momentum,
+                             running_mean, running_var, save, save + C, save + 2 * C, relu, comm,
+                             seq, stream);
+}
+
+extern "C" int b200dp_bn_backward(const void* dy, const void* x, const void* y_out, void* dx,
+                                  void* d_residual, int dtype, int64_t M, int C, const float* save,
+                                  const float* weight, const float* bias, int relu, void* scratch,
+                                  float* sums_local, float* grad_weight, float* grad_bias,
+                                  b200dp_comm* comm, uint32_t seq, b200dp_stream_t stream) {
+  if (!save) return B200DP_EINVAL;
+  int rc = b200dp_bn_bwd_reduce(dy, x, y_out, dtype, M, C, save, save + C, weight, bias, relu, scratch,
+                                sums_local, grad_weight, grad_bias, comm, seq, stream);
+  if (rc) return rc;
+  return b200dp_bn_bwd_apply(dy, x, y_out, dx, d_residual, dtype, M, C, save, save + C, weight, bias,
+                             sums_local, save + 2 * C, relu, comm, seq, stream);
+}

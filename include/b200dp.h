@@ -192,6 +192,24 @@ int b200dp_bn_bwd_apply(const void* dy, const void* x, const void* y_out,
                         int relu, b200dp_comm* comm, uint32_t seq,
                         b200dp_stream_t stream);
 
+/* Forward = b200dp_bn_fwd_stats + b200dp_bn_fwd_apply, backward = b200dp_bn_bwd_reduce +
+ * b200dp_bn_bwd_apply, each pair issued by ONE call (same kernels, same arguments; `save`
+ * is fp32 [2*C+1] = save_mean | save_invstd | save_count).  They stand for the whole of
+ * SyncBatchNorm.forward / .backward (TORCH/nn/modules/_functions.py:7-125 and :127-209) and
+ * exist because a foreign call from Python costs about as much as a small layer's kernel. */
+int b200dp_bn_forward(const void* x, const void* residual, void* y, int dtype,
+                      int64_t M, int C, void* scratch, float* stats_local,
+                      const float* weight, const float* bias, float eps,
+                      float momentum, float* running_mean, float* running_var,
+                      float* save, int relu, b200dp_comm* comm, uint32_t seq,
+                      b200dp_stream_t stream);
+int b200dp_bn_backward(const void* dy, const void* x, const void* y_out, void* dx,
+                       void* d_residual, int dtype, int64_t M, int C,
+                       const float* save, const float* weight, const float* bias,
+                       int relu, void* scratch, float* sums_local,
+                       float* grad_weight, float* grad_bias, b200dp_comm* comm,
+                       uint32_t seq, b200dp_stream_t stream);
+
 /* ------------------------------------------------------------------------
  * Communicator: library-owned symmetric buffers mapped into every rank.
  *
