@@ -196,13 +196,35 @@ class KernelProfiler:
         e0.record(s)
         rc = fn(*args)
         e1.record(s)
-        self.records.append((name, algorithmic_bytes(name, args), e0, e1))
+        shape = None
+        if name == "b200dp_bn_fwd_stats":
+            shape = (args[2], args[3])
+        elif name == "b200dp_bn_fwd_apply":
+            shape = (args[4], args[5], "res" if args[1] else "-")
+        elif name == "b200dp_bn_bwd_reduce":
+            shape = (args[4], args[5], f"mask{args[10]}")
+        elif name == "b200dp_bn_bwd_apply":
+            shape = (args[6], args[7], f"mask{args[14]}", "dres" if args[4] else "-")
+        self.records.append((name, algorithmic_bytes(name, args), e0, e1, shape))
         return rc
+
+    def detail(self):
+        """Per (kernel, layer shape): launches, mean microseconds, GB/s of algorithmic bytes."""
+        torch.cuda.synchronize()
+        out = {}
+        for name, nbytes, e0, e1, shape in self.records:
+            if shape is None:
+                continue
+            t = out.setdefault((name, shape), [0, 0.0, 0])
+            t[0] += 1
+            t[1] += e0.elapsed_time(e1)
+            t[2] += nbytes
+        return out
 
     def table(self):
         torch.cuda.synchronize()
         out = {}
-        for name, nbytes, e0, e1 in self.records:
+        for name, nbytes, e0, e1, _ in self.records:
             t = out.setdefault(name, {"launches": 0, "ms": 0.0, "bytes": 0})
             t["launches"] += 1
             t["ms"] += e0.elapsed_time(e1)
@@ -224,6 +246,7 @@ def main():
     ap.add_argument("--optimizer", default="sgd", choices=["sgd", "adam"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-kernel-pass", action="store_true")
+    ap.add_argument("--kernel-detail", default="", help="write per-layer-shape kernel timings of the kernel pass to this file")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -369,6 +392,10 @@ def main():
             step(dev_u8, dev_y)
         _lib.PROFILER = None
         table = prof.table()
+        if rank == 0 and args.kernel_detail:
+            with open(args.kernel_detail, "w") as f:
+                for (name, shape), (n, ms, nb) in sorted(prof.detail().items(), key=lambda kv: (kv[0][0], -kv[1][1])):
+                    f.write(f"{name:24s} {str(shape):32s} n={n:3d} {ms / n * 1e3:8.1f} us  {nb / ms / 1e6:7.0f} GB/s\n")
         if rank == 0:
             top = max((k for k in table if table[k]["bytes"] > 0), key=lambda k: table[k]["ms"])
             t = table[top]
