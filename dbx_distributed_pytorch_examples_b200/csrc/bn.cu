@@ -350,6 +350,14 @@ __device__ __forceinline__ uint4 lds128(uint32_t addr) {
   return r;
 }
 
+// Programmatic dependent launch (sm_90+): the reduction kernel lets its consumer start as soon
+// as every CTA has finished streaming, so the consumer's launch, its primed loads and the
+// first DRAM round trip overlap the reduction's serial tail; the consumer blocks in
+// pdl_wait() until the producer grid has completed and its writes are visible.  Both are
+// no-ops when the kernels are launched the ordinary way.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // rows this thread owns: first row, distance between its rows, how many
 struct RowRange {
   int64_t first, step;
@@ -511,6 +519,7 @@ bn_stats_kernel(const T* __restrict__ x, int64_t M, int C, void* scratch, float*
       }
     }
   }
+  pdl_launch_dependents();
   __syncthreads();  // every thread is done with its ring slots before the tree overwrites them
   cta_tree<N, true>(sA, sB, sN, n, mean, m2);
   if (!grid_merge<N, true>(scratch, C, c0, chan_ok, sA, sB, sN, n, mean, m2)) return;
@@ -580,6 +589,7 @@ __global__ void __launch_bounds__(kT, kOccFwd) bn_fwd_apply_kernel(FwdArgs A, b2
   ring.init(smem);
   const int nrows = chan_ok ? rr.count : 0;
   ring.prime(nrows, ptrs);
+  pdl_wait();  // statistics of the producer kernel are complete and visible from here on
 
   if (!A.given_mean && P.world > 1) wait_chunk(P, seq);
   if (tid < kCV && chan_ok) {  // r == 0: this thread's c0 is the group it publishes
@@ -770,6 +780,7 @@ bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T*
       for (int k = 0; k < N; ++k) s2[k] = fmaf(nmean[k], s1[k], s2[k]);
     }
   }
+  pdl_launch_dependents();
   __syncthreads();  // ring drained everywhere before the tree reuses the memory
   float dummy = 0.f;
   cta_tree<N, false>(sA, sB, nullptr, dummy, s1, s2);
@@ -831,6 +842,7 @@ __global__ void __launch_bounds__(kT, kOccBwd) bn_bwd_apply_kernel(BwdArgs A, b2
   ring.init(smem);
   const int nrows = chan_ok ? rr.count : 0;
   ring.prime(nrows, ptrs);  // in flight during the flag wait and the prologue
+  pdl_wait();
 
   if (P.world > 1) wait_chunk(P, seq);
   if (tid < kCV && chan_ok) {
@@ -927,6 +939,24 @@ __global__ void __launch_bounds__(kT, kOccBwd) bn_bwd_apply_kernel(BwdArgs A, b2
     }
   };
   ring.run(nrows, ptrs, proc);
+}
+
+// Launch with (or without) the programmatic-stream-serialization attribute.
+thread_local bool t_pdl_next = false;  // set by b200dp_bn_forward / _backward around their second launch
+
+template <typename... KArgs, typename... Args>
+cudaError_t launch_ex(void (*kernel)(KArgs...), dim3 grid, cudaStream_t s, bool pdl, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = dim3(kT, 1, 1);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
 }
 
 // ================================ host side ==================================
@@ -1049,10 +1079,13 @@ int launch_fwd_apply(const FwdArgs& A, bool relu, const b200dp_peers& P, uint32_
   const bool res = A.res != nullptr;
   const Grid2 g = plan_grid<T>(A.M, A.C, kOccFwd);
   const dim3 grid(g.gx, g.gy);
-  if (relu && res) bn_fwd_apply_kernel<T, true, true><<<grid, kT, 0, s>>>(A, P, seq);
-  else if (relu) bn_fwd_apply_kernel<T, true, false><<<grid, kT, 0, s>>>(A, P, seq);
-  else if (res) bn_fwd_apply_kernel<T, false, true><<<grid, kT, 0, s>>>(A, P, seq);
-  else bn_fwd_apply_kernel<T, false, false><<<grid, kT, 0, s>>>(A, P, seq);
+  const bool pdl = t_pdl_next;
+  cudaError_t e;
+  if (relu && res) e = launch_ex(bn_fwd_apply_kernel<T, true, true>, grid, s, pdl, A, P, seq);
+  else if (relu) e = launch_ex(bn_fwd_apply_kernel<T, true, false>, grid, s, pdl, A, P, seq);
+  else if (res) e = launch_ex(bn_fwd_apply_kernel<T, false, true>, grid, s, pdl, A, P, seq);
+  else e = launch_ex(bn_fwd_apply_kernel<T, false, false>, grid, s, pdl, A, P, seq);
+  if (e != cudaSuccess) return (int)e;
   B200DP_LAUNCH_CHECK();
   return B200DP_OK;
 }
@@ -1129,15 +1162,18 @@ int launch_bwd_apply(const BwdArgs& A, int relu, const b200dp_peers& P, uint32_t
   const Grid2 g = plan_grid<T>(A.M, A.C, kOccBwd);
   const dim3 grid(g.gx, g.gy);
   const bool dres = A.dres != nullptr;
+  const bool pdl = t_pdl_next;
+  cudaError_t e = cudaSuccess;
 #define B200DP_BWD_APPLY(R)                                                     \
   do {                                                                          \
-    if (dres) bn_bwd_apply_kernel<T, R, true><<<grid, kT, 0, s>>>(A, P, seq);   \
-    else bn_bwd_apply_kernel<T, R, false><<<grid, kT, 0, s>>>(A, P, seq);       \
+    if (dres) e = launch_ex(bn_bwd_apply_kernel<T, R, true>, grid, s, pdl, A, P, seq);   \
+    else e = launch_ex(bn_bwd_apply_kernel<T, R, false>, grid, s, pdl, A, P, seq);       \
   } while (0)
   if (relu == 0) B200DP_BWD_APPLY(0);
   else if (relu == 1) B200DP_BWD_APPLY(1);
   else B200DP_BWD_APPLY(2);
 #undef B200DP_BWD_APPLY
+  if (e != cudaSuccess) return (int)e;
   B200DP_LAUNCH_CHECK();
   return B200DP_OK;
 }
@@ -1199,9 +1235,12 @@ extern "C" int b200dp_bn_forward(const void* x, const void* residual, void* y, i
   if (!save) return B200DP_EINVAL;
   int rc = b200dp_bn_fwd_stats(x, dtype, M, C, scratch, stats_local, comm, seq, stream);
   if (rc) return rc;
-  return b200dp_bn_fwd_apply(x, residual, y, dtype, M, C, stats_local, weight, bias, eps, momentum,
-                             running_mean, running_var, save, save + C, save + 2 * C, relu, comm,
-                             seq, stream);
+  t_pdl_next = true;  // the normalise kernel may start while the statistics kernel finishes its tail
+  rc = b200dp_bn_fwd_apply(x, residual, y, dtype, M, C, stats_local, weight, bias, eps, momentum,
+                           running_mean, running_var, save, save + C, save + 2 * C, relu, comm, seq,
+                           stream);
+  t_pdl_next = false;
+  return rc;
 }
 
 extern "C" int b200dp_bn_backward(const void* dy, const void* x, const void* y_out, void* dx,
@@ -1213,6 +1252,9 @@ extern "C" int b200dp_bn_backward(const void* dy, const void* x, const void* y_o
   int rc = b200dp_bn_bwd_reduce(dy, x, y_out, dtype, M, C, save, save + C, weight, bias, relu, scratch,
                                 sums_local, grad_weight, grad_bias, comm, seq, stream);
   if (rc) return rc;
-  return b200dp_bn_bwd_apply(dy, x, y_out, dx, d_residual, dtype, M, C, save, save + C, weight, bias,
-                             sums_local, save + 2 * C, relu, comm, seq, stream);
+  t_pdl_next = true;
+  rc = b200dp_bn_bwd_apply(dy, x, y_out, dx, d_residual, dtype, M, C, save, save + C, weight, bias,
+                           sums_local, save + 2 * C, relu, comm, seq, stream);
+  t_pdl_next = false;
+  return rc;
 }

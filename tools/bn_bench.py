@@ -43,7 +43,7 @@ def main():
     scratch = torch.zeros(int(lib.b200dp_bn_scratch_bytes(0)), dtype=torch.uint8, device=dev)
     s = _lib.current_stream()
     totals = {}
-    print(f"{'C':>5} {'HW':>4} {'n':>2} {'res':>3} | " + " | ".join(f"{k:>22}" for k in ("stats", "fwd_apply", "bwd_reduce", "bwd_apply")))
+    print(f"{'C':>5} {'HW':>4} {'n':>2} {'res':>3} | " + " | ".join(f"{k:>22}" for k in ("stats", "fwd_apply", "bwd_reduce", "bwd_apply", "fwd(1 call)", "bwd(1 call)")))
     for C, HW, count, res in LAYERS:
         M = a.batch * HW * HW
         x = torch.randn(M, C, device=dev).to(dt)
@@ -69,6 +69,13 @@ def main():
                                                          P(w), P(b), P(sums), P(save) + 8 * C, mode, None, 0, s),
                           M * C * es * (5 if res else 3)),
         }
+        nb = lambda k: calls[k][1]  # noqa: E731
+        calls["fwd(1 call)"] = (lambda: lib.b200dp_bn_forward(P(x), P(r), P(y), code, M, C, P(scratch), P(stats), P(w), P(b),
+                                                             1e-5, 0.1, None, None, P(save), 1, None, 0, s),
+                                nb("stats") + nb("fwd_apply"))
+        calls["bwd(1 call)"] = (lambda: lib.b200dp_bn_backward(P(dy), P(x), P(y), P(dx), P(dr), code, M, C, P(save), P(w), P(b),
+                                                              mode, P(scratch), P(sums), P(gw), P(gb), None, 0, s),
+                                nb("bwd_reduce") + nb("bwd_apply"))
         cells = []
         for name, (fn, nbytes) in calls.items():
             for _ in range(2):
@@ -94,7 +101,8 @@ def main():
     print("per training step (all 53 layers):")
     for name, (ms, nbytes) in totals.items():
         print(f"  {name:10s} {ms:7.3f} ms  {nbytes/1e9:6.2f} GB  {nbytes/ms/1e6:6.0f} GB/s  {nbytes/ms/1e6/peak*100:4.1f}% of {peak:.0f} GB/s")
-    tot_ms = sum(v[0] for v in totals.values()); tot_b = sum(v[1] for v in totals.values())
+    four = ("stats", "fwd_apply", "bwd_reduce", "bwd_apply")
+    tot_ms = sum(totals[k][0] for k in four); tot_b = sum(totals[k][1] for k in four)
     print(f"  {'all':10s} {tot_ms:7.3f} ms  {tot_b/1e9:6.2f} GB  {tot_b/tot_ms/1e6:6.0f} GB/s  {tot_b/tot_ms/1e6/peak*100:4.1f}%")
 
 
