@@ -183,6 +183,16 @@ def algorithmic_bytes(name, a):
     return 0
 
 
+def traffic_for(entry):
+    """DRAM bytes (read + write) per launch of that kernel from the committed `ncu --set full` capture of
+    one training step (profiles/r1_traffic_*.json), or None when no capture exists for it."""
+    path = os.path.join(ROOT, "profiles", "r1_traffic_" + entry.replace("b200dp_", "") + ".json")
+    try:
+        return json.load(open(path))["traffic_bytes_per_launch"]
+    except Exception:
+        return None
+
+
 class KernelProfiler:
     def __init__(self):
         self.records = []
@@ -402,7 +412,8 @@ def main():
             achieved = t["bytes"] / (t["ms"] / 1e3) / 1e9
             step_ms = ms_dev / args.steps
             line["roofline"] = {"kernel": top, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                                "frac": achieved / peak, "traffic": None,
+                                "frac": achieved / peak, "traffic": traffic_for(top),
+                                "algorithmic_bytes_per_launch": t["bytes"] / max(t["launches"], 1),
                                 "launches_per_step": t["launches"] // 2, "ms_per_step": t["ms"] / 2,
                                 "share_of_step": t["ms"] / 2 / step_ms}
             line["kernels"] = {k: {"launches_per_step": v["launches"] // 2, "ms_per_step": round(v["ms"] / 2, 4),
