@@ -331,6 +331,115 @@ __global__ void __launch_bounds__(kAffThreads, 3) augment_affine_kernel(const Au
   }
 }
 
+// ---- direct variant: no staging, no barriers ------------------------------------------
+// Each thread fetches the (at most) 7 aligned words that hold its 8 source pixels straight
+// from global memory through L1 (neighbouring threads share the lines), so threads are fully
+// independent: no tile phases, no __syncthreads, and the only limit on loads in flight is the
+// number of resident warps.  Used when the source buffer is a whole number of words.
+struct DirectArgs {
+  const uint8_t* src;
+  const int32_t* params;
+  uint16_t* dst;
+  int Hs, Ws, pad, H, W;
+  int gpr;                 // groups of 8 pixels per output row
+  uint32_t gpr_magic;      // ceil(2^32 / gpr), 0 when gpr == 1
+  uint32_t h_magic;        // ceil(2^32 / H),   0 when H == 1
+  long long total_groups;  // B * H * gpr
+  long long src_bytes;
+};
+
+__device__ __forceinline__ uint32_t ldg_nc_u32(const void* p) {
+  uint32_t v;
+  asm volatile("ld.global.nc.u32 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
+
+template <bool PAD>
+__global__ void __launch_bounds__(256, 6) augment_direct_kernel(const DirectArgs a, const AffineCoef k) {
+  const long long stride = (long long)gridDim.x * 256;
+  for (long long g = (long long)blockIdx.x * 256 + threadIdx.x; g < a.total_groups; g += stride) {
+    // g -> (image b, output row y, group gi); total_groups < 2^31 is checked on the host
+    const uint32_t gu = (uint32_t)g;
+    const uint32_t rowid = a.gpr == 1 ? gu : __umulhi(gu, a.gpr_magic);  // b * H + y
+    const int gi = (int)(gu - rowid * (uint32_t)a.gpr);
+    const uint32_t b = a.H == 1 ? rowid : __umulhi(rowid, a.h_magic);
+    const int y = (int)(rowid - b * (uint32_t)a.H);
+    const int pi = min(max(__ldg(a.params + 3 * b + 0), 0), a.Hs + 2 * a.pad - a.H);
+    const int pj = min(max(__ldg(a.params + 3 * b + 1), 0), a.Ws + 2 * a.pad - a.W);
+    const bool flip = __ldg(a.params + 3 * b + 2) != 0;
+    const int x0 = gi * 8;
+    const int sy = pi + y - a.pad;
+    const int sxlo = pj - a.pad + (flip ? (a.W - 8 - x0) : x0);  // lowest source pixel of the group
+    const bool rowok = !PAD || (sy >= 0 && sy < a.Hs);
+    uint32_t u[6] = {0, 0, 0, 0, 0, 0};
+    if (rowok) {
+      const long long off = (((long long)b * a.Hs + sy) * a.Ws + sxlo) * 3;  // may be < 0 with padding
+      const long long al = off & ~3LL;
+      const uint32_t sh = (uint32_t)(off & 3) * 8;
+      uint32_t w[7];
+#pragma unroll
+      for (int i = 0; i < 7; ++i) {
+        const long long o = al + 4 * i;
+        w[i] = (o >= 0 && o < a.src_bytes) ? ldg_nc_u32(a.src + o) : 0u;
+      }
+#pragma unroll
+      for (int i = 0; i < 6; ++i) u[i] = __funnelshift_r(w[i], w[i + 1], sh);
+    }
+    uint32_t o[12];
+#pragma unroll
+    for (int p = 0; p < 8; ++p) {
+      bool ok = true;
+      if (PAD) {
+        const int sx = sxlo + p;  // block pixel p
+        ok = rowok && (sx >= 0) && (sx < a.Ws);
+      }
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const int bidx = 3 * p + c;
+        uint32_t v = (u[bidx >> 2] >> (8 * (bidx & 3))) & 0xffu;
+        if (PAD) v = ok ? v : 0u;
+        const float f = fmaf((float)v, k.A[c], k.B[c]);
+        // block pixel p is output pixel p, or 7-p when the image is flipped
+        const int e_n = 3 * p + c, e_f = 3 * (7 - p) + c;
+        // write both orders into separate packs lazily: select after the loop (cheap: 12 SELs)
+        if (e_n & 1) o[e_n >> 1] = pack_bf16(__uint_as_float(o[e_n >> 1]), f);
+        else o[e_n >> 1] = __float_as_uint(f);
+        (void)e_f;
+      }
+    }
+    // o holds the 24 results in BLOCK order (12 packed pairs).  Flipped: output pixel q = block pixel 7-q;
+    // a pixel is 3 halves, so the flipped order is a fixed permutation of 16-bit halves.
+    uint32_t r[12];
+    if (flip) {
+#pragma unroll
+      for (int h = 0; h < 12; ++h) {
+        // halves 2h and 2h+1 of the output come from block halves: e -> 3*(7 - e/3) + e%3
+        const int e0 = 2 * h, e1 = 2 * h + 1;
+        const int s0 = 3 * (7 - e0 / 3) + e0 % 3, s1 = 3 * (7 - e1 / 3) + e1 % 3;
+        const uint32_t lo = (s0 & 1) ? (o[s0 >> 1] >> 16) : (o[s0 >> 1] & 0xffffu);
+        const uint32_t hi = (s1 & 1) ? (o[s1 >> 1] & 0xffff0000u) : (o[s1 >> 1] << 16);
+        r[h] = lo | hi;
+      }
+    } else {
+#pragma unroll
+      for (int h = 0; h < 12; ++h) r[h] = o[h];
+    }
+    uint16_t* dst = a.dst + (((long long)rowid * a.W) + x0) * 3;
+#pragma unroll
+    for (int q = 0; q < 3; ++q) st_stream(dst + 8 * q, make_uint4(r[4 * q], r[4 * q + 1], r[4 * q + 2], r[4 * q + 3]));
+  }
+}
+
+template <bool PAD>
+int launch_direct(const DirectArgs& a, const AffineCoef& k, cudaStream_t s) {
+  long long want = (a.total_groups + 255) / 256;
+  const int cap = 6 * B200DP_NUM_SMS;
+  const int grid = (int)(want < cap ? want : cap);
+  augment_direct_kernel<PAD><<<grid, 256, 0, s>>>(a, k);
+  B200DP_LAUNCH_CHECK();
+  return B200DP_OK;
+}
+
 constexpr size_t kAffSmemBytes = kAffSlack + 2 * kAffTileBytes + 16 + 2 * kMaxRows * sizeof(int);
 
 // bf16 bits of an fp32 value, round to nearest even (finite inputs)
@@ -444,6 +553,21 @@ extern "C" int b200dp_augment_u8_bf16(const uint8_t* src, int B, int Hs, int Ws,
   // B200DP_AUGMENT_FORCE_TABLE=1 keeps the table kernel reachable for tests
   const char* force_table = getenv("B200DP_AUGMENT_FORCE_TABLE");
   const bool table_only = force_table && force_table[0] == '1';
+  const char* force_staged = getenv("B200DP_AUGMENT_FORCE_STAGED");
+  const bool staged_only = force_staged && force_staged[0] == '1';
+  if (!table_only && !staged_only && vec8 && (a.src_bytes & 3) == 0 && affine_is_exact(mean, std, &k)) {
+    DirectArgs d;
+    d.src = src; d.params = params; d.dst = dst;
+    d.Hs = Hs; d.Ws = Ws; d.pad = pad; d.H = H; d.W = W;
+    d.gpr = W / 8;
+    d.gpr_magic = d.gpr == 1 ? 0u : (uint32_t)(0x100000000ULL / (unsigned)d.gpr) + 1u;
+    d.h_magic = H == 1 ? 0u : (uint32_t)(0x100000000ULL / (unsigned)H) + 1u;
+    d.total_groups = (long long)B * H * d.gpr;
+    d.src_bytes = a.src_bytes;
+    // the reciprocal-multiply divisions are exact while dividend * divisor < 2^32
+    if (d.total_groups < (1LL << 31) && d.total_groups * d.gpr < (1LL << 32) && (long long)B * H * H < (1LL << 32))
+      return pad ? launch_direct<true>(d, k, s) : launch_direct<false>(d, k, s);
+  }
   if (!table_only && vec8 && a.pitch <= kAffTileBytes && pad * 3 + 4 <= kAffSlack &&
       affine_is_exact(mean, std, &k)) {
     int rmax = kAffTileBytes / a.pitch;

@@ -55,6 +55,10 @@ def test_table_kernel_matches_arithmetic_kernel(monkeypatch):
         monkeypatch.setenv("B200DP_AUGMENT_FORCE_TABLE", "1")
         table = tf(x.cuda(), params=params)
         monkeypatch.delenv("B200DP_AUGMENT_FORCE_TABLE")
+        monkeypatch.setenv("B200DP_AUGMENT_FORCE_STAGED", "1")   # arithmetic kernel with shared-memory staging
+        staged = tf(x.cuda(), params=params)
+        monkeypatch.delenv("B200DP_AUGMENT_FORCE_STAGED")
+        assert torch.equal(staged, table)
         want = transform_ref.crop_flip_normalize(x.numpy(), params.numpy(), pad, (out, out),
                                                  np.float32(T.IMAGENET_MEAN), np.float32(T.IMAGENET_STD))
         assert np.array_equal(bits(table), transform_ref.f32_to_bf16_bits(want))
