@@ -286,8 +286,8 @@ __device__ __forceinline__ bool grid_merge(void* scratch, int C, int chbase, boo
   return true;
 }
 
-// Store this rank's chunk of an exchange vector into every rank's slot and
-// raise the chunk flag.  Called by the whole electing CTA; `a`/`b`/`cnt` are
+// Store this rank's chunk of an exchange vector into every rank's slot as LL words
+// {value, seq} (see b200dp_sync_area).  Called by the whole electing CTA; `a`/`b`/`cnt` are
 // valid in threads with r == 0.
 template <int N>
 __device__ __forceinline__ void push_chunk(const b200dp_peers& P, uint32_t seq, int C, int c0,
@@ -298,26 +298,40 @@ __device__ __forceinline__ void push_chunk(const b200dp_peers& P, uint32_t seq, 
   const int by = blockIdx.y;
   if (r == 0 && chan_ok) {
     for (int p = 0; p < P.world; ++p) {
-      float* d = P.sync[p]->bn_data[slot][P.rank];
+      uint2* d = P.sync[p]->bn_ll[slot][P.rank];
 #pragma unroll
       for (int k = 0; k < N; ++k) {
-        d[c0 + k] = a[k];
-        d[C + c0 + k] = b[k];
+        st_ll(d + c0 + k, a[k], seq);
+        st_ll(d + C + c0 + k, b[k], seq);
       }
-      if (tid == 0) d[2 * B200DP_BN_MAX_CHANNELS + by] = cnt;
+      if (tid == 0) st_ll(d + 2 * B200DP_BN_MAX_CHANNELS + by, cnt, seq);
     }
-    __threadfence_system();
   }
-  __syncthreads();
-  if (tid < P.world) st_release_sys(&P.sync[tid]->bn_flag[slot][P.rank][by], seq);
 }
 
-// Wait until every rank's chunk `by` of exchange `seq` has landed here.
-__device__ __forceinline__ void wait_chunk(const b200dp_peers& P, uint32_t seq) {
+// world*kCV threads poll the ranks' LL words of this chunk side by side and put the values
+// into shared memory (xr[rank][cv][2N+1 (+pad)]); the kCV coefficient threads then merge
+// from shared memory in rank order.
+constexpr int kXrStride = 20;  // floats per (rank, cv): 2*8 + 1 used, padded to a multiple of 4
+template <int N>
+__device__ __forceinline__ void wait_and_gather(const b200dp_peers& P, uint32_t seq, int C, float* xr) {
   const int slot = seq % B200DP_XCHG_SLOTS;
-  if (threadIdx.x < P.world) {
-    if (!wait_flag(&P.sync[P.rank]->bn_flag[slot][threadIdx.x][blockIdx.y], seq))
-      atomicExch(&P.sync[P.rank]->error, 1u);
+  const int tid = threadIdx.x;
+  if (tid < P.world * kCV) {
+    const int p = tid / kCV, cv = tid % kCV;
+    const int c0 = blockIdx.y * (kCV * N) + cv * N;
+    if (c0 < C) {
+      const uint2* d = P.sync[P.rank]->bn_ll[slot][p];
+      float* o = xr + (p * kCV + cv) * kXrStride;
+      bool ok = true;
+#pragma unroll
+      for (int k = 0; k < N; ++k) {
+        ok &= ld_ll(d + c0 + k, seq, o + k);
+        ok &= ld_ll(d + C + c0 + k, seq, o + N + k);
+      }
+      ok &= ld_ll(d + 2 * B200DP_BN_MAX_CHANNELS + blockIdx.y, seq, o + 2 * N);
+      if (!ok) atomicExch(&P.sync[P.rank]->error, 1u);
+    }
   }
   __syncthreads();
 }
@@ -591,7 +605,8 @@ __global__ void __launch_bounds__(kT, kOccFwd) bn_fwd_apply_kernel(FwdArgs A, b2
   ring.prime(nrows, ptrs);
   pdl_wait();  // statistics of the producer kernel are complete and visible from here on
 
-  if (!A.given_mean && P.world > 1) wait_chunk(P, seq);
+  __shared__ __align__(16) float xr[B200DP_MAX_WORLD * kCV * kXrStride];
+  if (!A.given_mean && P.world > 1) wait_and_gather<N>(P, seq, C, xr);
   if (tid < kCV && chan_ok) {  // r == 0: this thread's c0 is the group it publishes
     float mean[N], a[N], b[N];
     if (A.given_mean) {
@@ -607,17 +622,9 @@ __global__ void __launch_bounds__(kT, kOccFwd) bn_fwd_apply_kernel(FwdArgs A, b2
 #pragma unroll
       for (int k = 0; k < N; ++k) mean[k] = m2[k] = 0.f;
       if (P.world > 1) {
-        const int slot = seq % B200DP_XCHG_SLOTS;
-        for (int p = 0; p < P.world; ++p) {
-          const float* d = P.sync[P.rank]->bn_data[slot][p];
-          float om[N], oq[N];
-#pragma unroll
-          for (int k = 0; k < N; ++k) {
-            om[k] = ld_cg_f32(d + c0 + k);
-            oq[k] = ld_cg_f32(d + C + c0 + k);
-          }
-          const float on = ld_cg_f32(d + 2 * B200DP_BN_MAX_CHANNELS + blockIdx.y);
-          welford_merge<N>(n, mean, m2, on, om, oq);
+        for (int p = 0; p < P.world; ++p) {  // rank order: every rank computes identical statistics
+          const float* o = xr + (p * kCV + cv) * kXrStride;
+          welford_merge<N>(n, mean, m2, o[2 * N], o, o + N);
         }
       } else {
         n = ld_cg_f32(A.stats_local + 2 * C);
@@ -844,19 +851,19 @@ __global__ void __launch_bounds__(kT, kOccBwd) bn_bwd_apply_kernel(BwdArgs A, b2
   ring.prime(nrows, ptrs);  // in flight during the flag wait and the prologue
   pdl_wait();
 
-  if (P.world > 1) wait_chunk(P, seq);
+  __shared__ __align__(16) float xr[B200DP_MAX_WORLD * kCV * kXrStride];
+  if (P.world > 1) wait_and_gather<N>(P, seq, C, xr);
   if (tid < kCV && chan_ok) {
     float s1[N], s2[N];
 #pragma unroll
     for (int k = 0; k < N; ++k) s1[k] = s2[k] = 0.f;
     if (P.world > 1) {
-      const int slot = seq % B200DP_XCHG_SLOTS;
       for (int p = 0; p < P.world; ++p) {
-        const float* d = P.sync[P.rank]->bn_data[slot][p];
+        const float* o = xr + (p * kCV + cv) * kXrStride;
 #pragma unroll
         for (int k = 0; k < N; ++k) {
-          s1[k] += ld_cg_f32(d + c0 + k);
-          s2[k] += ld_cg_f32(d + C + c0 + k);
+          s1[k] += o[k];
+          s2[k] += o[N + k];
         }
       }
     } else {

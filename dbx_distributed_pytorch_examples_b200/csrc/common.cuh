@@ -81,6 +81,22 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
+__device__ __forceinline__ void st_ll(uint2* p, float v, uint32_t seq) {
+  asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(__float_as_uint(v)), "r"(seq) : "memory");
+}
+// Poll an LL word until it carries `seq`; false on timeout (~10 s).
+__device__ __forceinline__ bool ld_ll(const uint2* p, uint32_t seq, float* out) {
+  uint32_t a, b;
+  long long t0 = 0;
+  while (true) {
+    asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(a), "=r"(b) : "l"(p) : "memory");
+    if (b == seq) break;
+    if (t0 == 0) t0 = clock64();
+    if (clock64() - t0 > (20LL << 30)) { *out = 0.f; return false; }
+  }
+  *out = __uint_as_float(a);
+  return true;
+}
 // Spin until *p has reached `seq` (wrap-safe).  Returns false on timeout so a
 // dead peer turns into an error flag instead of a hung GPU.
 __device__ __forceinline__ bool wait_flag(const uint32_t* p, uint32_t seq) {
@@ -185,9 +201,6 @@ __host__ __device__ __forceinline__ bool aligned16(const void* p) {
 #define B200DP_BUCKET_FLAG_SLOTS 64
 
 struct b200dp_sync_area {
-  // SyncBN exchange: flag[slot][src_rank][chunk] = seq once that chunk of
-  // src_rank's vector for exchange `seq` has landed in data[slot][src_rank].
-  uint32_t bn_flag[B200DP_XCHG_SLOTS][B200DP_MAX_WORLD][B200DP_BN_MAX_CHUNKS];
   // Gradient buckets: ready = "my bucket is packed", done = "I finished
   // reading/writing everybody's slice".
   uint32_t ready[B200DP_BUCKET_FLAG_SLOTS][B200DP_MAX_WORLD];
@@ -196,7 +209,10 @@ struct b200dp_sync_area {
   uint32_t error;  // set by a kernel whose flag wait timed out
   uint32_t pad_[7];
   uint32_t ticket[B200DP_BUCKET_FLAG_SLOTS];  // local "last CTA" elections (self-resetting)
-  float bn_data[B200DP_XCHG_SLOTS][B200DP_MAX_WORLD][B200DP_XCHG_FLOATS];
+  // SyncBN exchange, "LL" style: every 8-byte word is {float bits, seq}.  A word is valid for
+  // exchange `seq` once its second half equals seq; 8-byte stores are atomic, so no fence and
+  // no separate flag are needed and the exchange costs one NVLink traversal.
+  uint2 bn_ll[B200DP_XCHG_SLOTS][B200DP_MAX_WORLD][B200DP_XCHG_FLOATS];
 };
 
 struct b200dp_comm {

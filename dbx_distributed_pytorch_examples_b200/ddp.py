@@ -175,6 +175,7 @@ class B200DDP(DistributedDataParallel):
         self._opt_step_count = 0
         self._comm_hook = None
         self._iteration_armed = False
+        self._bcast_buffers = None
         self.bucket_bytes_cap = int((25 if bucket_cap_mb is None else bucket_cap_mb) * 1024 * 1024)
 
         if dist.is_available() and dist.is_initialized():
@@ -248,7 +249,9 @@ class B200DDP(DistributedDataParallel):
     def forward(self, *inputs, **kwargs):
         if self.world > 1 and self.broadcast_buffers and self.require_forward_param_sync:
             # buffers of B200SyncBatchNorm layers are identical on all ranks by construction
-            for buf in self._needs_buffer_broadcast():
+            if self._bcast_buffers is None:  # computed once: the module tree does not change between steps
+                self._bcast_buffers = self._needs_buffer_broadcast()
+            for buf in self._bcast_buffers:
                 dist.broadcast(buf, src=0, group=self.process_group)
         if torch.is_grad_enabled() and self.require_backward_grad_sync:
             self._arm_iteration()
