@@ -170,11 +170,11 @@ def algorithmic_bytes(name, a):
     if name == "b200dp_bn_fwd_stats":
         return a[2] * a[3] * es(a[1])
     if name == "b200dp_bn_fwd_apply":
-        return a[4] * a[5] * es(a[3]) * (2 + (1 if a[1] else 0))
+        return a[4] * a[5] * es(a[3]) * (2 + (1 if a[1] else 0) + (0.25 if len(a) > 20 and a[20] else 0))
     if name == "b200dp_bn_bwd_reduce":
-        return a[4] * a[5] * es(a[3]) * (2 + (1 if a[10] == 2 else 0))
+        return a[4] * a[5] * es(a[3]) * (2 + {2: 1, 3: 0.25}.get(a[10], 0))
     if name == "b200dp_bn_bwd_apply":
-        return a[6] * a[7] * es(a[5]) * (3 + (1 if a[14] == 2 else 0) + (1 if a[4] else 0))
+        return a[6] * a[7] * es(a[5]) * (3 + {2: 1, 3: 0.25}.get(a[14], 0) + (1 if a[4] else 0))
     if name == "b200dp_augment_u8_bf16":
         return a[1] * a[6] * a[7] * 3 * 3
     if name == "b200dp_allreduce_update":  # world 1: g + master r/w + momentum r/w + param copy

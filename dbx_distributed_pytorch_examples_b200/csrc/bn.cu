@@ -385,7 +385,7 @@ __device__ __forceinline__ RowRange my_rows(int64_t M, int r) {
   return rr;
 }
 
-template <int D, int NS, bool EVICT_FIRST>
+template <int D, int NS, bool EVICT_FIRST, bool W2 = false>  // W2: stream 2 carries one 32-bit word per row
 struct RowRing {
   uint32_t base;  // shared-space address of this thread's slot (stream 0, depth 0)
   uint64_t pol;
@@ -398,12 +398,14 @@ struct RowRing {
     if (EVICT_FIRST) {
       cp_async16_evict_first(slot(d, 0), p0, pol);
       if (NS > 1) cp_async16_evict_first(slot(d, 1), p1, pol);
-      if (NS > 2) cp_async16_evict_first(slot(d, 2), p2, pol);
+      if (NS > 2 && !W2) cp_async16_evict_first(slot(d, 2), p2, pol);
     } else {
       cp_async16(slot(d, 0), p0);
       if (NS > 1) cp_async16(slot(d, 1), p1);
-      if (NS > 2) cp_async16(slot(d, 2), p2);
+      if (NS > 2 && !W2) cp_async16(slot(d, 2), p2);
     }
+    if (NS > 2 && W2)
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(slot(d, 2)), "l"(p2) : "memory");
   }
   // Fill the ring with the first rows; one commit group per row, always D groups.
   template <typename PtrF>
@@ -426,7 +428,8 @@ struct RowRing {
       cp_async_wait<D - 1>();  // the group of row k has landed
       uint4 v0 = lds128(slot(d, 0)), v1, v2;
       if (NS > 1) v1 = lds128(slot(d, 1));
-      if (NS > 2) v2 = lds128(slot(d, 2));
+      if (NS > 2 && !W2) v2 = lds128(slot(d, 2));
+      if (NS > 2 && W2) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v2.x) : "r"(slot(d, 2)));
       proc(k, v0, v1, v2);     // consumes the values: the slot may be overwritten after this
       if (k + D < nrows) {
         const void *p0, *p1, *p2;
@@ -456,6 +459,15 @@ __device__ __forceinline__ void sts_vec(float* p, const float* in) {
 #pragma unroll
   for (int k = 0; k < N; k += 4) *reinterpret_cast<float4*>(p + k) = make_float4(in[k], in[k + 1], in[k + 2], in[k + 3]);
 }
+// lanes of a packed bf16 pair kept (0xffff) or cleared (0) by bits 2j and 2j+1 of a ReLU mask word
+__device__ __forceinline__ uint32_t pair_keep(uint32_t bits, int j) {
+  return ((bits >> (2 * j)) & 1u) * 0xffffu | ((bits >> (2 * j + 1)) & 1u) * 0xffff0000u;
+}
+__device__ __forceinline__ uint4 apply_mask_word(const uint4& g, uint32_t bits) {
+  return make_uint4(g.x & pair_keep(bits, 0), g.y & pair_keep(bits, 1), g.z & pair_keep(bits, 2),
+                    g.w & pair_keep(bits, 3));
+}
+
 template <typename T>
 struct is_bf16 { static constexpr bool value = false; };
 template <>
@@ -568,6 +580,8 @@ struct FwdArgs {
   // inference: use these instead of batch statistics
   const float* given_mean;
   const float* given_var;
+  // optional output: one 32-bit word per 16-byte vector of y, bit j = (y[j] > 0)
+  uint32_t* maskw;
 };
 
 // Per-channel coefficients of one chunk are worked out once per CTA, by its first kCV
@@ -689,13 +703,27 @@ __global__ void __launch_bounds__(kT, kOccFwd) bn_fwd_apply_kernel(FwdArgs A, b2
       }
     }
     // y is read again by the next convolution: leave it in L2
-    *reinterpret_cast<uint4*>(yb + off0 + k * step) = Vec<T>::pack(f);
+    const uint4 pk = Vec<T>::pack(f);
+    *reinterpret_cast<uint4*>(yb + off0 + k * step) = pk;
+    if constexpr (RELU && is_bf16<T>::value) {
+      if (A.maskw) {  // post-ReLU halves are >= +0: positive <=> non-zero
+        const uint32_t w[4] = {pk.x, pk.y, pk.z, pk.w};
+        uint32_t bits = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          bits |= ((w[j] & 0xffffu) != 0u ? 1u : 0u) << (2 * j);
+          bits |= ((w[j] >> 16) != 0u ? 1u : 0u) << (2 * j + 1);
+        }
+        A.maskw[(off0 + k * step) >> 3] = bits;  // element offset / 8 = vector index
+      }
+    }
   };
   ring.run(nrows, ptrs, proc);
 }
 
 // ============================= backward: reduce ==============================
-// RELU: 0 none, 1 mask recomputed from x (no residual was fused), 2 mask from y.
+// RELU: 0 none, 1 mask recomputed from x (no residual was fused), 2 mask from y,
+// 3 (bf16) mask from the forward's bit words (one uint32 per 16-byte vector; `yo` points at them).
 template <typename T, int RELU>
 __global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kT, kOccFwd)
 bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T* __restrict__ yo,
@@ -703,7 +731,7 @@ bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T*
                      const float* weight, const float* bias, void* scratch, float* sums_local,
                      float* grad_weight, float* grad_bias, b200dp_peers P, uint32_t seq) {
   constexpr int N = Vec<T>::N;
-  using Ring = RowRing<RELU == 2 ? 3 : 4, RELU == 2 ? 3 : 2, false>;  // 32 or 36 KiB (static smem limit 48 KiB)
+  using Ring = RowRing<RELU >= 2 ? 3 : 4, RELU >= 2 ? 3 : 2, false, RELU == 3>;  // 32 or 36 KiB (static smem limit 48 KiB)
   constexpr int kTreeBytes = 2 * N * kT * 4;
   __shared__ __align__(16) unsigned char smem[Ring::kBytes > kTreeBytes ? Ring::kBytes : kTreeBytes];
   float* sA = reinterpret_cast<float*>(smem);
@@ -721,7 +749,9 @@ bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T*
     auto ptrs = [&](int k, const void*& p0, const void*& p1, const void*& p2) {
       p0 = dy + off0 + k * step;
       p1 = x + off0 + k * step;
-      p2 = RELU == 2 ? (const void*)(yo + off0 + k * step) : nullptr;
+      p2 = RELU == 2   ? (const void*)(yo + off0 + k * step)
+           : RELU == 3 ? (const void*)(reinterpret_cast<const uint32_t*>(yo) + ((off0 + k * step) >> 3))
+                       : nullptr;
     };
     Ring ring;
     ring.init(smem);
@@ -753,6 +783,7 @@ bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T*
           g.z = bf16x2_mul(vg.z, bf16x2_gt0_mask(vy.z));
           g.w = bf16x2_mul(vg.w, bf16x2_gt0_mask(vy.w));
         }
+        if (RELU == 3) g = apply_mask_word(vg, vy.x);
 #pragma unroll
         for (int k = 0; k < N; ++k) {
           const uint16_t gh = vec_half(g, k), xh = vec_half(vx, k);
@@ -825,7 +856,7 @@ struct BwdArgs {
 template <typename T, int RELU, bool DRES>
 __global__ void __launch_bounds__(kT, kOccBwd) bn_bwd_apply_kernel(BwdArgs A, b200dp_peers P, uint32_t seq) {
   constexpr int N = Vec<T>::N;
-  using Ring = RowRing<RELU == 2 ? 3 : 4, RELU == 2 ? 3 : 2, true>;
+  using Ring = RowRing<RELU >= 2 ? 3 : 4, RELU >= 2 ? 3 : 2, true, RELU == 3>;
   __shared__ __align__(16) unsigned char smem[Ring::kBytes];
   __shared__ __align__(16) float coef[5][kChunkMax];  // -mean, a, b, -mean_dy, -k
   const int tid = threadIdx.x, r = tid / kCV, cv = tid % kCV;
@@ -843,7 +874,9 @@ __global__ void __launch_bounds__(kT, kOccBwd) bn_bwd_apply_kernel(BwdArgs A, b2
   auto ptrs = [&](int k, const void*& p0, const void*& p1, const void*& p2) {
     p0 = dyb + off0 + k * step;
     p1 = xb + off0 + k * step;
-    p2 = RELU == 2 ? (const void*)(yob + off0 + k * step) : nullptr;
+    p2 = RELU == 2   ? (const void*)(yob + off0 + k * step)
+         : RELU == 3 ? (const void*)(reinterpret_cast<const uint32_t*>(yob) + ((off0 + k * step) >> 3))
+                     : nullptr;
   };
   Ring ring;
   ring.init(smem);
@@ -910,6 +943,7 @@ __global__ void __launch_bounds__(kT, kOccBwd) bn_bwd_apply_kernel(BwdArgs A, b2
         g.z = bf16x2_mul(vg.z, bf16x2_gt0_mask(vy.z));
         g.w = bf16x2_mul(vg.w, bf16x2_gt0_mask(vy.w));
       }
+      if (RELU == 3) g = apply_mask_word(vg, vy.x);
       float gm[N];
 #pragma unroll
       for (int j = 0; j < N; ++j) {
@@ -1104,14 +1138,15 @@ extern "C" int b200dp_bn_fwd_apply(const void* x, const void* residual, void* y,
                                    float momentum, float* running_mean, float* running_var,
                                    float* save_mean, float* save_invstd, float* save_count,
                                    int relu, b200dp_comm* comm, uint32_t seq,
-                                   b200dp_stream_t stream) {
+                                   b200dp_stream_t stream, uint32_t* relu_mask) {
   int rc = check_common(x, residual, y, dtype, M, C);
   if (rc) return rc;
+  if (relu_mask && (dtype != B200DP_BF16 || !relu)) return B200DP_EUNSUPPORTED;
   if (!stats_local || !save_mean || !save_invstd || !save_count) return B200DP_EINVAL;
   if (M > 0 && !y) return B200DP_EINVAL;
   if ((rc = check_comm(comm, seq))) return rc;
   FwdArgs A{x, residual, y, M, C, stats_local, weight, bias, eps, momentum, running_mean,
-            running_var, save_mean, save_invstd, save_count, nullptr, nullptr};
+            running_var, save_mean, save_invstd, save_count, nullptr, nullptr, relu_mask};
   const b200dp_peers P = b200dp_make_peers(comm);
   cudaStream_t s = (cudaStream_t)stream;
   return dtype == B200DP_BF16 ? launch_fwd_apply<__nv_bfloat16>(A, relu != 0, P, seq, s)
@@ -1129,7 +1164,7 @@ extern "C" int b200dp_bn_inference(const void* x, const void* residual, void* y,
   if (M == 0) return B200DP_OK;
   if (!y) return B200DP_EINVAL;
   FwdArgs A{x, residual, y, M, C, nullptr, weight, bias, eps, 0.f, nullptr, nullptr, nullptr,
-            nullptr, nullptr, running_mean, running_var};
+            nullptr, nullptr, running_mean, running_var, nullptr};
   const b200dp_peers P = b200dp_make_peers(nullptr);
   cudaStream_t s = (cudaStream_t)stream;
   return dtype == B200DP_BF16 ? launch_fwd_apply<__nv_bfloat16>(A, relu != 0, P, 0, s)
@@ -1145,7 +1180,8 @@ int launch_bwd_reduce(const void* dy, const void* x, const void* yo, int64_t M, 
                       cudaStream_t s) {
   const int maxc = relu == 0   ? max_active_clusters(bn_bwd_reduce_kernel<T, 0>)
                    : relu == 1 ? max_active_clusters(bn_bwd_reduce_kernel<T, 1>)
-                               : max_active_clusters(bn_bwd_reduce_kernel<T, 2>);
+                   : relu == 2 ? max_active_clusters(bn_bwd_reduce_kernel<T, 2>)
+                               : max_active_clusters(bn_bwd_reduce_kernel<T, 3>);
   const Grid2 g = plan_grid_clustered<T>(M, C, maxc);
   const dim3 grid(g.gx, g.gy);
   const T* pdy = static_cast<const T*>(dy);
@@ -1157,7 +1193,8 @@ int launch_bwd_reduce(const void* dy, const void* x, const void* yo, int64_t M, 
                                                  grad_weight, grad_bias, P, seq)
   if (relu == 0) B200DP_BWD_REDUCE(0);
   else if (relu == 1) B200DP_BWD_REDUCE(1);
-  else B200DP_BWD_REDUCE(2);
+  else if (relu == 2) B200DP_BWD_REDUCE(2);
+  else B200DP_BWD_REDUCE(3);
 #undef B200DP_BWD_REDUCE
   B200DP_LAUNCH_CHECK();
   return B200DP_OK;
@@ -1178,7 +1215,8 @@ int launch_bwd_apply(const BwdArgs& A, int relu, const b200dp_peers& P, uint32_t
   } while (0)
   if (relu == 0) B200DP_BWD_APPLY(0);
   else if (relu == 1) B200DP_BWD_APPLY(1);
-  else B200DP_BWD_APPLY(2);
+  else if (relu == 2) B200DP_BWD_APPLY(2);
+  else B200DP_BWD_APPLY(3);
 #undef B200DP_BWD_APPLY
   if (e != cudaSuccess) return (int)e;
   B200DP_LAUNCH_CHECK();
@@ -1194,8 +1232,9 @@ extern "C" int b200dp_bn_bwd_reduce(const void* dy, const void* x, const void* y
                                     b200dp_comm* comm, uint32_t seq, b200dp_stream_t stream) {
   int rc = check_common(dy, x, y_out, dtype, M, C);
   if (rc) return rc;
-  if (relu < 0 || relu > 2) return B200DP_EINVAL;
-  if (M > 0 && (!x || (relu == 2 && !y_out))) return B200DP_EINVAL;
+  if (relu < 0 || relu > 3) return B200DP_EINVAL;
+  if (relu == 3 && dtype != B200DP_BF16) return B200DP_EUNSUPPORTED;
+  if (M > 0 && (!x || (relu >= 2 && !y_out))) return B200DP_EINVAL;
   if (!save_mean || !save_invstd || !scratch || !sums_local) return B200DP_EINVAL;
   if ((rc = check_comm(comm, seq))) return rc;
   const b200dp_peers P = b200dp_make_peers(comm);
@@ -1218,8 +1257,9 @@ extern "C" int b200dp_bn_bwd_apply(const void* dy, const void* x, const void* y_
   int rc = check_common(dy, x, dx, dtype, M, C);
   if (rc) return rc;
   if (!aligned16(y_out) || !aligned16(d_residual)) return B200DP_EALIGN;
-  if (relu < 0 || relu > 2) return B200DP_EINVAL;
-  if (M > 0 && (!x || !dx || (relu == 2 && !y_out))) return B200DP_EINVAL;
+  if (relu < 0 || relu > 3) return B200DP_EINVAL;
+  if (relu == 3 && dtype != B200DP_BF16) return B200DP_EUNSUPPORTED;
+  if (M > 0 && (!x || !dx || (relu >= 2 && !y_out))) return B200DP_EINVAL;
   if (!save_mean || !save_invstd || !sums_local || !save_count) return B200DP_EINVAL;
   if ((rc = check_comm(comm, seq))) return rc;
   BwdArgs A{dy, x, y_out, dx, d_residual, M, C, save_mean, save_invstd, weight, bias,
@@ -1238,14 +1278,14 @@ extern "C" int b200dp_bn_forward(const void* x, const void* residual, void* y, i
                                  int C, void* scratch, float* stats_local, const float* weight,
                                  const float* bias, float eps, float momentum, float* running_mean,
                                  float* running_var, float* save, int relu, b200dp_comm* comm,
-                                 uint32_t seq, b200dp_stream_t stream) {
+                                 uint32_t seq, b200dp_stream_t stream, uint32_t* relu_mask) {
   if (!save) return B200DP_EINVAL;
   int rc = b200dp_bn_fwd_stats(x, dtype, M, C, scratch, stats_local, comm, seq, stream);
   if (rc) return rc;
   t_pdl_next = true;  // the normalise kernel may start while the statistics kernel finishes its tail
   rc = b200dp_bn_fwd_apply(x, residual, y, dtype, M, C, stats_local, weight, bias, eps, momentum,
                            running_mean, running_var, save, save + C, save + 2 * C, relu, comm, seq,
-                           stream);
+                           stream, relu_mask);
   t_pdl_next = false;
   return rc;
 }

@@ -151,7 +151,10 @@ int b200dp_bn_fwd_apply(const void* x, const void* residual, void* y, int dtype,
                         float momentum, float* running_mean, float* running_var,
                         float* save_mean, float* save_invstd, float* save_count,
                         int relu, b200dp_comm* comm, uint32_t seq,
-                        b200dp_stream_t stream);
+                        b200dp_stream_t stream, uint32_t* relu_mask);
+/* relu_mask (may be NULL; BF16 with relu != 0 only): M*C/8 words, one per 16-byte vector
+ * of y, bit j set when y[j] > 0.  The backward entry points read it in mode relu == 3
+ * (pass it as y_out) instead of re-reading y: 0.5 B instead of 2 B per element and pass. */
 
 /* Eval-mode batch norm from running statistics (F.batch_norm(training=False),
  * TORCH/nn/modules/batchnorm.py:818-828) with the same fused epilogues. */
@@ -166,7 +169,8 @@ int b200dp_bn_inference(const void* x, const void* residual, void* y, int dtype,
  *   relu == 1  the mask is recomputed from x as (x-mean)*invstd*weight+bias > 0
  *              (only valid when no residual was fused; costs no extra bytes);
  *   relu == 2  the mask is y_out > 0, y_out being the forward OUTPUT (read only
- *              in this mode; may be NULL otherwise).
+ *              in this mode; may be NULL otherwise);
+ *   relu == 3  (BF16) y_out points at the relu_mask words written by the forward.
  * sums_local[2*C] = sum g, sum g*(x-mean); grad_weight = sum g*(x-mean)*invstd
  * and grad_bias = sum g from the LOCAL sums (DDP averages them later); either
  * may be NULL.  weight / bias may be NULL (affine=False: 1 and 0).  With
@@ -202,7 +206,7 @@ int b200dp_bn_forward(const void* x, const void* residual, void* y, int dtype,
                       const float* weight, const float* bias, float eps,
                       float momentum, float* running_mean, float* running_var,
                       float* save, int relu, b200dp_comm* comm, uint32_t seq,
-                      b200dp_stream_t stream);
+                      b200dp_stream_t stream, uint32_t* relu_mask);
 int b200dp_bn_backward(const void* dy, const void* x, const void* y_out, void* dx,
                        void* d_residual, int dtype, int64_t M, int C,
                        const float* save, const float* weight, const float* bias,

@@ -86,6 +86,24 @@ def test_against_torch_batch_norm(dtype):
         torch.testing.assert_close(bn.bias.grad, br.grad, rtol=1e-3, atol=1e-2)
 
 
+def test_mask_word_mode_equals_mask_from_y(monkeypatch):
+    """Opt-in backward for residual layers that reads the forward's ReLU bit words instead of y: same bits out."""
+    from dbx_distributed_pytorch_examples_b200 import syncbn
+    torch.manual_seed(3)
+    shape = (6, 128, 9, 9)
+    mk = lambda: torch.randn(shape, device="cuda").bfloat16().contiguous(memory_format=torch.channels_last)  # noqa: E731
+    x, res, dy = mk(), mk(), mk()
+    w, b = torch.rand(128, device="cuda") + 0.5, torch.randn(128, device="cuda")
+    rm, rv = torch.zeros(128, device="cuda"), torch.ones(128, device="cuda")
+    outs = []
+    for flag in (False, True):
+        monkeypatch.setattr(syncbn, "_USE_MASK_WORDS", flag)
+        bn, y, dx, dres = run_ours(x, res, dy, w, b, rm, rv, True)
+        outs.append((y, dx, dres, bn.weight.grad.clone(), bn.bias.grad.clone()))
+    for a, c in zip(*outs):
+        assert torch.equal(a, c)
+
+
 def test_eval_mode_and_nchw_input_and_2d():
     torch.manual_seed(1)
     ref = torch.nn.BatchNorm2d(64).cuda()

@@ -55,25 +55,26 @@ def main():
         stats = torch.empty(2 * C + 1, device=dev)
         save = torch.empty(2 * C + 1, device=dev)
         sums, gw, gb = torch.empty(2 * C, device=dev), torch.empty(C, device=dev), torch.empty(C, device=dev)
-        mode = 2 if res else 1
+        mode = 3 if res else 1
+        mk = torch.empty(M * C // 8, dtype=torch.int32, device=dev) if res else None
         P = lambda t: 0 if t is None else t.data_ptr()  # noqa: E731
         calls = {
             "stats": (lambda: lib.b200dp_bn_fwd_stats(P(x), code, M, C, P(scratch), P(stats), None, 0, s), M * C * es),
             "fwd_apply": (lambda: lib.b200dp_bn_fwd_apply(P(x), P(r), P(y), code, M, C, P(stats), P(w), P(b), 1e-5, 0.1,
-                                                         None, None, P(save), P(save) + 4 * C, P(save) + 8 * C, 1, None, 0, s),
-                          M * C * es * (3 if res else 2)),
-            "bwd_reduce": (lambda: lib.b200dp_bn_bwd_reduce(P(dy), P(x), P(y), code, M, C, P(save), P(save) + 4 * C, P(w), P(b),
+                                                         None, None, P(save), P(save) + 4 * C, P(save) + 8 * C, 1, None, 0, s, P(mk)),
+                          M * C * es * (3.25 if res else 2)),
+            "bwd_reduce": (lambda: lib.b200dp_bn_bwd_reduce(P(dy), P(x), P(mk if res else y), code, M, C, P(save), P(save) + 4 * C, P(w), P(b),
                                                            mode, P(scratch), P(sums), P(gw), P(gb), None, 0, s),
-                           M * C * es * (3 if res else 2)),
-            "bwd_apply": (lambda: lib.b200dp_bn_bwd_apply(P(dy), P(x), P(y), P(dx), P(dr), code, M, C, P(save), P(save) + 4 * C,
+                           M * C * es * (2.25 if res else 2)),
+            "bwd_apply": (lambda: lib.b200dp_bn_bwd_apply(P(dy), P(x), P(mk if res else y), P(dx), P(dr), code, M, C, P(save), P(save) + 4 * C,
                                                          P(w), P(b), P(sums), P(save) + 8 * C, mode, None, 0, s),
-                          M * C * es * (5 if res else 3)),
+                          M * C * es * (4.25 if res else 3)),
         }
         nb = lambda k: calls[k][1]  # noqa: E731
         calls["fwd(1 call)"] = (lambda: lib.b200dp_bn_forward(P(x), P(r), P(y), code, M, C, P(scratch), P(stats), P(w), P(b),
-                                                             1e-5, 0.1, None, None, P(save), 1, None, 0, s),
+                                                             1e-5, 0.1, None, None, P(save), 1, None, 0, s, P(mk)),
                                 nb("stats") + nb("fwd_apply"))
-        calls["bwd(1 call)"] = (lambda: lib.b200dp_bn_backward(P(dy), P(x), P(y), P(dx), P(dr), code, M, C, P(save), P(w), P(b),
+        calls["bwd(1 call)"] = (lambda: lib.b200dp_bn_backward(P(dy), P(x), P(mk if res else y), P(dx), P(dr), code, M, C, P(save), P(w), P(b),
                                                               mode, P(scratch), P(sums), P(gw), P(gb), None, 0, s),
                                 nb("bwd_reduce") + nb("bwd_apply"))
         cells = []

@@ -38,14 +38,15 @@ def main():
         stats, save = torch.empty(2 * C + 1, device=dev), torch.empty(2 * C + 1, device=dev)
         sums, gw, gb = torch.empty(2 * C, device=dev), torch.empty(C, device=dev), torch.empty(C, device=dev)
         P = lambda t: 0 if t is None else t.data_ptr()  # noqa: E731
-        mode = 2 if res else 1
+        mode = 3 if res else 1
+        mk = torch.empty(M * C // 8, dtype=torch.int32, device=dev) if res else None
         for _ in range(a.reps):
             _lib.check(lib.b200dp_bn_fwd_stats(P(x), 1, M, C, P(scratch), P(stats), None, 0, s))
             _lib.check(lib.b200dp_bn_fwd_apply(P(x), P(r), P(y), 1, M, C, P(stats), P(w), P(b), 1e-5, 0.1, None, None,
-                                               P(save), P(save) + 4 * C, P(save) + 8 * C, 1, None, 0, s))
-            _lib.check(lib.b200dp_bn_bwd_reduce(P(dy), P(x), P(y), 1, M, C, P(save), P(save) + 4 * C, P(w), P(b), mode,
+                                               P(save), P(save) + 4 * C, P(save) + 8 * C, 1, None, 0, s, P(mk)))
+            _lib.check(lib.b200dp_bn_bwd_reduce(P(dy), P(x), P(mk if res else y), 1, M, C, P(save), P(save) + 4 * C, P(w), P(b), mode,
                                                 P(scratch), P(sums), P(gw), P(gb), None, 0, s))
-            _lib.check(lib.b200dp_bn_bwd_apply(P(dy), P(x), P(y), P(dx), P(dr), 1, M, C, P(save), P(save) + 4 * C,
+            _lib.check(lib.b200dp_bn_bwd_apply(P(dy), P(x), P(mk if res else y), P(dx), P(dr), 1, M, C, P(save), P(save) + 4 * C,
                                                P(w), P(b), P(sums), P(save) + 8 * C, mode, None, 0, s))
         torch.cuda.synchronize()
     print("done")
