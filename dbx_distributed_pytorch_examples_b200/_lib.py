@@ -53,6 +53,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if not force and os.path.exists(LIB_PATH):
         newest = max(os.path.getmtime(p) for p in srcs + hdrs if os.path.exists(p))
         if os.path.getmtime(LIB_PATH) >= newest:
+            build_fastcall()
             return LIB_PATH
     nvcc = os.environ.get("NVCC", "nvcc")
     cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_PATH] + srcs
@@ -61,7 +62,28 @@ def build(force: bool = False, verbose: bool = False) -> str:
         raise B200DPError("nvcc failed:\n" + proc.stdout + proc.stderr)
     if verbose:
         print(proc.stderr)
+    build_fastcall(force=True)
     return LIB_PATH
+
+
+def _fast_path() -> str:
+    import sysconfig
+
+    return os.path.join(PKG_DIR, "_b200dp_fast" + sysconfig.get_config_var("EXT_SUFFIX"))
+
+
+def build_fastcall(force: bool = False) -> str:
+    """gcc-compile csrc/fastcall.c (CPython METH_FASTCALL shim for the per-layer SyncBN calls)."""
+    import sysconfig
+
+    src, out = os.path.join(CSRC_DIR, "fastcall.c"), _fast_path()
+    if not force and os.path.exists(out) and os.path.getmtime(out) >= os.path.getmtime(src):
+        return out
+    cmd = [os.environ.get("CC", "gcc"), "-O2", "-shared", "-fPIC", "-I" + sysconfig.get_paths()["include"], "-o", out, src]
+    proc = subprocess.run(cmd, capture_output=True, text=True, stdin=subprocess.DEVNULL, timeout=300)
+    if proc.returncode != 0:
+        raise B200DPError("gcc failed on fastcall.c:\n" + proc.stdout + proc.stderr)
+    return out
 
 
 _lock = threading.Lock()
@@ -164,6 +186,30 @@ def lib():
                 fn.argtypes = args
             _lib = _Handle(handle)
     return _lib
+
+
+_fast = None
+
+
+def fast():
+    """The fast-call shim bound to the loaded library, or None when it has not been built
+    (callers then use ctypes: same C ABI, ~10 us more per call)."""
+    global _fast
+    if _fast is None:
+        path = _fast_path()
+        if not os.path.exists(path):
+            _fast = False
+        else:
+            import importlib.util
+
+            spec = importlib.util.spec_from_file_location("_b200dp_fast", path)
+            mod = importlib.util.module_from_spec(spec)
+            spec.loader.exec_module(mod)
+            cdll = lib()._cdll
+            mod.bind(ctypes.cast(cdll.b200dp_bn_forward, c_void_p).value,
+                     ctypes.cast(cdll.b200dp_bn_backward, c_void_p).value)
+            _fast = mod
+    return _fast or None
 
 
 def check(rc: int, what: str = "") -> None:

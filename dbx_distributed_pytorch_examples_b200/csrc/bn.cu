@@ -187,32 +187,37 @@ __device__ __forceinline__ void cta_tree(float* sA, float* sB, float* sN, float&
 template <int N, bool WELFORD>
 __device__ __forceinline__ bool grid_merge(void* scratch, int C, int chbase, bool chan_ok,
                                            float* sA, float* sB, float* sN, float& n, float* a,
-                                           float* b) {
+                                           float* b, cg::cluster_group::arrival_token&& started) {
   __shared__ bool is_last;
-  __shared__ __align__(16) float xchg[kCV][2 * N + 4];  // read by the cluster leader over DSMEM
+  // the leader's copy is written by all CTAs of the cluster (DSMEM stores), one row per CTA rank
+  __shared__ __align__(16) float xchg[kCluster][kCV][2 * N + 4];
   const int tid = threadIdx.x, r = tid / kCV;
   cg::cluster_group cluster = cg::this_cluster();
-  if (r == 0) {
+  const unsigned rank = cluster.block_rank();
+  // every CTA of the cluster arrived on this barrier when it started: DSMEM of the leader exists
+  cluster.barrier_wait(std::move(started));
+  if (r == 0 && rank != 0) {  // push: nobody waits on a remote read, and one cluster barrier is enough
+    float* dst = cluster.map_shared_rank(&xchg[rank][tid][0], 0);
 #pragma unroll
     for (int k = 0; k < N; ++k) {
-      xchg[tid][k] = a[k];
-      xchg[tid][N + k] = b[k];
+      dst[k] = a[k];
+      dst[N + k] = b[k];
     }
-    xchg[tid][2 * N] = n;
+    dst[2 * N] = n;
   }
-  cluster.sync();
-  const bool leader = cluster.block_rank() == 0;
-  if (leader && r == 0) {
+  cluster.sync();  // release/acquire at cluster scope: the pushed values are visible to the leader
+  if (rank != 0) return false;
+  if (r == 0) {
     for (unsigned q = 1; q < kCluster; ++q) {
-      const float* rem = cluster.map_shared_rank(&xchg[tid][0], q);
+      const float* src = &xchg[q][tid][0];
       float oa[N], ob[N];
 #pragma unroll
       for (int k = 0; k < N; ++k) {
-        oa[k] = rem[k];
-        ob[k] = rem[N + k];
+        oa[k] = src[k];
+        ob[k] = src[N + k];
       }
       if (WELFORD) {
-        welford_merge<N>(n, a, b, rem[2 * N], oa, ob);
+        welford_merge<N>(n, a, b, src[2 * N], oa, ob);
       } else {
 #pragma unroll
         for (int k = 0; k < N; ++k) {
@@ -222,8 +227,6 @@ __device__ __forceinline__ bool grid_merge(void* scratch, int C, int chbase, boo
       }
     }
   }
-  cluster.sync();  // the others' shared memory must stay alive until the leader has read it
-  if (!leader) return false;
 
   unsigned int* tickets = reinterpret_cast<unsigned int*>((char*)scratch + kScratchTickets);
   float* counts = reinterpret_cast<float*>((char*)scratch + kScratchCounts);
@@ -490,6 +493,7 @@ bn_stats_kernel(const T* __restrict__ x, int64_t M, int C, void* scratch, float*
   const int tid = threadIdx.x, r = tid / kCV, cv = tid % kCV;
   const int c0 = blockIdx.y * (kCV * N) + cv * N;
   const bool chan_ok = c0 < C;
+  auto started = cg::this_cluster().barrier_arrive();  // waited on just before the DSMEM push
 
   float n = 0.f, mean[N], m2[N];
 #pragma unroll
@@ -548,7 +552,7 @@ bn_stats_kernel(const T* __restrict__ x, int64_t M, int C, void* scratch, float*
   pdl_launch_dependents();
   __syncthreads();  // every thread is done with its ring slots before the tree overwrites them
   cta_tree<N, true>(sA, sB, sN, n, mean, m2);
-  if (!grid_merge<N, true>(scratch, C, c0, chan_ok, sA, sB, sN, n, mean, m2)) return;
+  if (!grid_merge<N, true>(scratch, C, c0, chan_ok, sA, sB, sN, n, mean, m2, std::move(started))) return;
 
   if (r == 0 && chan_ok) {
 #pragma unroll
@@ -739,6 +743,7 @@ bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T*
   const int tid = threadIdx.x, r = tid / kCV, cv = tid % kCV;
   const int c0 = blockIdx.y * (kCV * N) + cv * N;
   const bool chan_ok = c0 < C;
+  auto started = cg::this_cluster().barrier_arrive();  // waited on just before the DSMEM push
 
   float s1[N], s2[N];
 #pragma unroll
@@ -822,7 +827,7 @@ bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T*
   __syncthreads();  // ring drained everywhere before the tree reuses the memory
   float dummy = 0.f;
   cta_tree<N, false>(sA, sB, nullptr, dummy, s1, s2);
-  if (!grid_merge<N, false>(scratch, C, c0, chan_ok, sA, sB, nullptr, dummy, s1, s2)) return;
+  if (!grid_merge<N, false>(scratch, C, c0, chan_ok, sA, sB, nullptr, dummy, s1, s2, std::move(started))) return;
 
   if (r == 0 && chan_ok) {
 #pragma unroll

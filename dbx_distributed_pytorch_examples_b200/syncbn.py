@@ -129,7 +129,14 @@ class _FusedSyncBN(torch.autograd.Function):
             if _USE_MASK_WORDS and relu and residual is not None and dt == _lib.BF16 and torch.is_grad_enabled():
                 maskw = torch.empty(x.numel() // 8, dtype=torch.int32, device=dev)
             mp = 0 if maskw is None else maskw.data_ptr()
-            if _lib.PROFILER is None:
+            fast = _lib.fast()
+            if _lib.PROFILER is None and fast is not None:
+                _lib.CALLS["b200dp_bn_forward"] = _lib.CALLS.get("b200dp_bn_forward", 0) + 1
+                rc = fast.bn_forward(xp, rp, yp, dt, M, C, scr, aux_p, wp, bp, float(eps), float(momentum), rmp, rvp, sv,
+                                     int(bool(relu)), h.value if h else 0, seq, stream, mp)
+                if rc:
+                    _lib.check(rc, "b200dp_bn_forward")
+            elif _lib.PROFILER is None:
                 _lib.check(lib.b200dp_bn_forward(xp, rp, yp, dt, M, C, scr, aux_p, wp, bp, float(eps), float(momentum),
                                                  rmp, rvp, sv, int(bool(relu)), h, seq, stream, mp), "b200dp_bn_forward")
             else:  # per-kernel timing pass: the same two launches through their own entry points
@@ -174,7 +181,14 @@ class _FusedSyncBN(torch.autograd.Function):
             gwp = out_p + 8 * C if weight is not None else 0
             gbp = out_p + 12 * C if bias is not None else 0
             scr = _bn_scratch(idx, stream)
-            if _lib.PROFILER is None:
+            fast = _lib.fast()
+            if _lib.PROFILER is None and fast is not None:
+                _lib.CALLS["b200dp_bn_backward"] = _lib.CALLS.get("b200dp_bn_backward", 0) + 1
+                rc = fast.bn_backward(dyp, xp, yp, dxp, drp, dt, M, C, sv, wp, bp, ctx.relu_mode, scr, out_p, gwp, gbp,
+                                      h.value if h else 0, seq, stream)
+                if rc:
+                    _lib.check(rc, "b200dp_bn_backward")
+            elif _lib.PROFILER is None:
                 _lib.check(lib.b200dp_bn_backward(dyp, xp, yp, dxp, drp, dt, M, C, sv, wp, bp, ctx.relu_mode, scr,
                                                   out_p, gwp, gbp, h, seq, stream), "b200dp_bn_backward")
             else:
