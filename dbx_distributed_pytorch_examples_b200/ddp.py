@@ -425,15 +425,18 @@ class B200DDP(DistributedDataParallel):
         self._state_stale = False
         optimizer.register_state_dict_pre_hook(self._check_state_consolidated)
 
-        def step(closure=None):
+        def step(opt_self, closure=None):
             loss = closure() if closure is not None else None
             if ddp._opt_kind == _lib.OPT_ADAM:
                 for a in ddp._arenas:
                     for p in a.params:
-                        optimizer.state[p]["step"] += 1
+                        opt_self.state[p]["step"] += 1
             return loss
 
-        optimizer.step = step
+        # a bound method, like the one it replaces: LR schedulers wrap optimizer.step and look at
+        # its __func__ / __self__ (torch/optim/lr_scheduler.py, patch_track_step_called)
+        import types
+        optimizer.step = types.MethodType(step, optimizer)
         return optimizer
 
     def _opt_args(self, arena) -> _lib.OptArgs:

@@ -151,3 +151,61 @@ def test_comm_hook_compat():
     x, y = batch(0)
     F.cross_entropy(ddp(x), y).backward()
     assert [s[0] for s in seen] == [0, 1, 2] and seen[-1][1] and sum(s[3] for s in seen) == 62
+
+
+def test_unused_parameter_no_sync_and_lr_schedule():
+    """A parameter that gets no gradient, gradient accumulation under no_sync(), and an LR scheduler driving
+    the fused update: all against the same steps in plain torch."""
+    class Net(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.a, self.b, self.unused = torch.nn.Linear(64, 256), torch.nn.Linear(256, 10), torch.nn.Linear(8, 8)
+
+        def forward(self, x):
+            return self.b(torch.relu(self.a(x)))
+
+    torch.manual_seed(0)
+    ref = Net().cuda()
+    m = copy.deepcopy(ref)
+    ddp = b200.B200DDP(m, device_ids=[0], find_unused_parameters=True)
+    o_ref = torch.optim.SGD(ref.parameters(), lr=0.1, momentum=0.9)
+    o_our = ddp.fuse_optimizer(torch.optim.SGD(ddp.parameters(), lr=0.1, momentum=0.9))
+    s_ref = torch.optim.lr_scheduler.StepLR(o_ref, step_size=1, gamma=0.5)
+    s_our = torch.optim.lr_scheduler.StepLR(o_our, step_size=1, gamma=0.5)
+    g = torch.Generator().manual_seed(1)
+    for step in range(4):
+        xs = [torch.randn(16, 64, generator=g).cuda() for _ in range(2)]
+        ys = [torch.randint(0, 10, (16,), generator=g).cuda() for _ in range(2)]
+        o_ref.zero_grad(); o_our.zero_grad()
+        for x, y in zip(xs, ys):                      # reference: two micro-batches accumulate
+            F.cross_entropy(ref(x), y).backward()
+        with ddp.no_sync():                           # ours: first micro-batch stays local ...
+            F.cross_entropy(ddp(xs[0]), ys[0]).backward()
+        F.cross_entropy(ddp(xs[1]), ys[1]).backward()  # ... the second one reduces and updates
+        o_ref.step(); o_our.step(); s_ref.step(); s_our.step()
+    assert o_our.param_groups[0]["lr"] == o_ref.param_groups[0]["lr"] == 0.1 * 0.5 ** 4
+    for (n, a), b in zip(ref.named_parameters(), m.parameters()):
+        torch.testing.assert_close(b, a, rtol=1e-5, atol=1e-6, msg=lambda s: f"{n}: {s}")
+    assert torch.equal(m.unused.weight, ref.unused.weight)  # untouched on both sides
+
+
+def test_feed_and_loss_reader():
+    """ShardedBatchSampler -> PinnedImageDataset -> DeviceFeeder -> BatchTransform, losses read one step late."""
+    n = 50
+    images = torch.randint(0, 256, (n, 12, 12, 3), dtype=torch.uint8)
+    labels = torch.arange(n)
+    ds = b200.PinnedImageDataset(images, labels)
+    sampler = b200.ShardedBatchSampler(n, 16, rank=0, world=1, seed=3)
+    tf = b200.BatchTransform(8)
+    reader = b200.LossReader()
+    seen, fed = [], []
+    for img, lab in b200.DeviceFeeder(ds.batches(sampler)):
+        assert img.is_cuda and img.dtype == torch.uint8 and lab.is_cuda
+        assert torch.equal(img.cpu(), images[lab.cpu()])          # the right rows arrived
+        out = tf(img, generator=torch.Generator().manual_seed(0))
+        assert out.shape == (len(lab), 3, 8, 8)
+        fed.append(float(lab.float().mean()))
+        reader.push(lab.float().mean())
+        seen.extend(lab.cpu().tolist())
+    assert sorted(seen) == list(range(n))
+    assert reader.flush() == pytest.approx(fed)
