@@ -9,6 +9,7 @@ Three drop-ins for a torch DDP ResNet train loop
 * :class:`B200SyncBatchNorm` / :func:`convert_sync_batchnorm` /
   :func:`fuse_bn_relu` — SyncBatchNorm with fused (+residual)+ReLU, NHWC;
 * :class:`BatchTransform` — uint8 NHWC -> crop/flip/normalize -> bf16 in one kernel.
+* :class:`ResizeBatchTransform` — the same with Pillow's bilinear resize (Resize / RandomResizedCrop).
 
 All arithmetic runs in libb200dp.so (hand-written sm_100a CUDA behind the C ABI
 of include/b200dp.h).  There is no CPU or eager fallback: without the built
@@ -21,10 +22,11 @@ from .distributor import DeepspeedTorchDistributor, TorchDistributor  # noqa: F4
 from .feed import DeviceFeeder, LossReader, PinnedImageDataset, ShardedBatchSampler  # noqa: F401
 from .fusion import fuse_bn_relu  # noqa: F401
 from .syncbn import B200SyncBatchNorm, convert_sync_batchnorm  # noqa: F401
-from .transform import BatchTransform, draw_crop_flip_params  # noqa: F401
+from .transform import (BatchTransform, ResizeBatchTransform, draw_crop_flip_params,  # noqa: F401
+                        draw_resized_crop_flip_params)
 
 __all__ = [
     "B200DDP", "prepare_model", "B200SyncBatchNorm", "BatchTransform", "Communicator", "TorchDistributor",
-    "DeepspeedTorchDistributor", "convert_sync_batchnorm", "fuse_bn_relu", "draw_crop_flip_params",
+    "DeepspeedTorchDistributor", "convert_sync_batchnorm", "fuse_bn_relu", "draw_crop_flip_params", "ResizeBatchTransform", "draw_resized_crop_flip_params",
     "B200DPError", "build", "DeviceFeeder", "LossReader", "PinnedImageDataset", "ShardedBatchSampler",
 ]

@@ -15,6 +15,8 @@ per-sample loop would have left it.  Checked against the loop in tests/test_host
 """
 from __future__ import annotations
 
+import math
+
 import numpy as np
 import torch
 
@@ -94,3 +96,74 @@ def crop_flip_draws(n: int, range_i: int, range_j: int, flip_p: float, generator
     uniform = (u & np.uint32(0xFFFFFF)).astype(np.float32) * np.float32(2.0 ** -24)
     out[:, 2] = (uniform < np.float32(flip_p)).astype(np.int32)
     return out
+
+
+def _peek_uint32(generator, count: int):
+    """(saved state, next ``count`` outputs); the caller rewinds with ``set_state(saved)``."""
+    gen = generator if generator is not None else torch.default_generator
+    saved = gen.get_state()
+    return gen, saved, take_uint32(gen, count)
+
+
+def resized_crop_flip_draws(n: int, height: int, width: int, scale=(0.08, 1.0), ratio=(3.0 / 4.0, 4.0 / 3.0),
+                            flip_p: float = 0.5, generator=None) -> np.ndarray:
+    """int32 [n, 5] = (i, j, h, w, flip): n sequential ``RandomResizedCrop.get_params`` +
+    ``RandomHorizontalFlip`` draws (TV/transforms/transforms.py:929-970, :720) from one stream.
+
+    Per try torchvision consumes one word for ``empty(1).uniform_(scale)`` and one for
+    ``exp(empty(1).uniform_(log ratio))``; an accepted try consumes two more (randint i, j);
+    the flip consumes one.  ATen's float uniform is ``(word & (2**24-1)) * 2**-24`` in double,
+    then ``* (to - from) + from`` (to/from rounded to float32), rounded to float32.  The number
+    of words used depends on the data, so a block is read ahead, walked, and the generator
+    is then advanced by exactly what the walk consumed.
+    """
+    area = height * width
+    log_ratio = torch.log(torch.tensor(ratio))  # float32, as torchvision builds it
+    s0, s1 = np.float32(scale[0]), np.float32(scale[1])
+    r0, r1 = np.float32(float(log_ratio[0])), np.float32(float(log_ratio[1]))
+    out = np.zeros((n, 5), dtype=np.int32)
+    block = 23 * n  # worst case per sample: 10 rejected tries (2 words each) + i, j + flip
+    while True:
+        gen, saved, raw = _peek_uint32(generator, block)
+        u = (raw & np.uint32(0xFFFFFF)).astype(np.float64) * (2.0 ** -24)
+        as_scale = (u * np.float64(s1 - s0) + np.float64(s0)).astype(np.float32).astype(np.float64).tolist()
+        as_logr = (u * np.float64(r1 - r0) + np.float64(r0)).astype(np.float32)
+        as_ratio = torch.exp(torch.from_numpy(as_logr)).numpy().astype(np.float64).tolist()  # torch's own float32 exp
+        as_flip = (u.astype(np.float32) < np.float32(flip_p)).tolist()
+        raw64 = raw.tolist()  # python ints: the walk below is scalar
+        p, ok = 0, True
+        for k in range(n):
+            if p + 23 > block:  # worst case: 10 tries + flip
+                ok = False
+                break
+            done = False
+            for _ in range(10):
+                target_area = area * as_scale[p]
+                aspect = as_ratio[p + 1]
+                p += 2
+                w = int(round(math.sqrt(target_area * aspect)))
+                h = int(round(math.sqrt(target_area / aspect)))
+                if 0 < w <= width and 0 < h <= height:
+                    i = raw64[p] % (height - h + 1)
+                    j = raw64[p + 1] % (width - w + 1)
+                    p += 2
+                    done = True
+                    break
+            if not done:  # central crop fallback
+                in_ratio = float(width) / float(height)
+                if in_ratio < min(ratio):
+                    w = width
+                    h = int(round(w / min(ratio)))
+                elif in_ratio > max(ratio):
+                    h = height
+                    w = int(round(h * max(ratio)))
+                else:
+                    w, h = width, height
+                i, j = (height - h) // 2, (width - w) // 2
+            out[k] = (i, j, h, w, int(as_flip[p]))
+            p += 1
+        gen.set_state(saved)
+        if ok:
+            take_uint32(gen, p)
+            return out
+        block *= 3

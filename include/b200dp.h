@@ -84,6 +84,32 @@ int b200dp_augment_u8_bf16(const uint8_t* src, int B, int Hs, int Ws,
                            const float* mean, const float* std, uint16_t* dst,
                            b200dp_stream_t stream);
 
+/* (3b) Input transform with a resize: uint8 NHWC -> crop box -> bilinear resize ->
+ *      h-flip -> normalize -> bf16 NHWC, one launch per batch.
+ *
+ * Replaces the per-sample PIL path of transforms.Resize((S, S)) + RandomHorizontalFlip +
+ * ToTensor + Normalize (utils/hf_dataset_utilities.py:64-79) and of
+ * transforms.RandomResizedCrop(224) + ... (02_deepspeed/03_1k_imagenet_deepspeed_resnet.py:
+ * 45-53).  For PIL images torchvision's resized_crop is img.crop + img.resize(BILINEAR)
+ * (TV/transforms/functional.py resized_crop -> TV/transforms/_functional_pil.py resize), so
+ * the resize is Pillow's two-pass fixed-point resampler (Pillow src/libImaging/Resample.c,
+ * 22-bit coefficients, uint8 intermediate): the uint8 result is reproduced bit for bit and
+ * then normalised exactly as in (3).
+ *
+ *  src     uint8 [B, Hs, Ws, 3], device memory (or mapped pinned host memory)
+ *  params  int32 [B, 5] = (top i, left j, height h, width w, flip) per sample: the box
+ *          RandomResizedCrop.get_params returns (TV/transforms/transforms.py:929-970) or
+ *          (0, 0, Hs, Ws, flip) for a plain Resize; device or pinned host.  A box outside
+ *          the slab is moved / shrunk into it on the device (torchvision never makes one).
+ *  dst     bf16 [B, H, W, 3], 16-byte aligned
+ *  mean,std  HOST pointers to 3 floats each
+ * B200DP_EUNSUPPORTED when one output row's source span does not fit shared memory
+ * (down-scaling by more than ~200x); B200DP_ETOOBIG for B > 65535. */
+int b200dp_resized_crop_u8_bf16(const uint8_t* src, int B, int Hs, int Ws,
+                                const int32_t* params, int H, int W,
+                                const float* mean, const float* std, uint16_t* dst,
+                                b200dp_stream_t stream);
+
 /* ------------------------------------------------------------------------
  * (2) SyncBatchNorm, NHWC ([M, C] row-major, M = N*H*W), training mode.
  *

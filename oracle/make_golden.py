@@ -55,6 +55,42 @@ def gen_transform(name, B, src_hw, out, pad, mean, std, seed):
                         out_f32=out_nhwc.numpy(), out_bf16=bf16_bits(out_nhwc), seed=seed)
 
 
+def gen_resample(name, B, src_hw, out, random_resized_crop, mean, std, seed):
+    """Resize / RandomResizedCrop on PIL images through torchvision itself
+    (utils/hf_dataset_utilities.py:64-79; 02_deepspeed/03_1k_imagenet_deepspeed_resnet.py:45-53)."""
+    from PIL import Image
+    from torchvision import transforms as T
+    from torchvision.transforms import functional as TF
+
+    rng = np.random.default_rng(seed)
+    hs, ws = src_hw
+    # smooth-ish content plus noise, so that rounding cases of the resampler differ from pure noise
+    base = rng.integers(0, 256, size=(B, (hs + 7) // 8, (ws + 7) // 8, 3), dtype=np.uint8)
+    src = np.repeat(np.repeat(base, 8, axis=1), 8, axis=2)[:, :hs, :ws, :].astype(np.int32)
+    src = np.clip(src + rng.integers(-40, 41, size=src.shape), 0, 255).astype(np.uint8)
+    first = T.RandomResizedCrop(out) if random_resized_crop else T.Resize((out, out))
+    pipeline = T.Compose([first, T.RandomHorizontalFlip(), T.ToTensor(), T.Normalize(mean, std)])
+    torch.manual_seed(seed)
+    outs = torch.stack([pipeline(Image.fromarray(src[b])) for b in range(B)]).permute(0, 2, 3, 1).contiguous()
+    # the same draws through torchvision's own get_params, to record them, and the uint8 stage
+    torch.manual_seed(seed)
+    params = np.zeros((B, 5), dtype=np.int32)
+    resized = np.zeros((B, out, out, 3), dtype=np.uint8)
+    for b in range(B):
+        img = Image.fromarray(src[b])
+        if random_resized_crop:
+            i, j, h, w = T.RandomResizedCrop.get_params(img, [0.08, 1.0], [3.0 / 4.0, 4.0 / 3.0])
+        else:
+            i, j, h, w = 0, 0, hs, ws
+        flip = bool(torch.rand(1) < 0.5)
+        params[b] = (i, j, h, w, int(flip))
+        resized[b] = np.asarray(TF.resized_crop(img, i, j, h, w, [out, out]))  # before the flip
+    np.savez_compressed(os.path.join(GOLD, name), src=src, params=params, out_hw=out,
+                        mean=np.asarray(mean, np.float64), std=np.asarray(std, np.float64),
+                        resized_u8=resized, out_bf16=bf16_bits(outs), seed=seed,
+                        random_resized_crop=int(random_resized_crop))
+
+
 def gen_syncbn():
     torch.manual_seed(7)
     C, eps, mom = 16, 1e-5, 0.1
@@ -216,9 +252,20 @@ if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--skip-ddp", action="store_true")
     ap.add_argument("--only-ddp", action="store_true")
+    ap.add_argument("--only-resample", action="store_true")
     ap.add_argument("--steps", type=int, default=200)
     a = ap.parse_args()
     os.makedirs(GOLD, exist_ok=True)
+    imagenet = ((0.485, 0.456, 0.406), (0.229, 0.224, 0.225))
+    if not a.only_ddp:
+        # RandomResizedCrop (02_deepspeed/03_1k_imagenet_deepspeed_resnet.py:45-53) at fixture size and at
+        # the full 256 -> 224 size; Resize((64, 64)) of 32x32 images (utils/hf_dataset_utilities.py:64-66)
+        gen_resample("resample_rrc56.npz", 12, (96, 80), 56, True, *imagenet, 2024)
+        gen_resample("resample_rrc224.npz", 2, (256, 256), 224, True, *imagenet, 7)
+        gen_resample("resample_resize64.npz", 6, (32, 32), 64, False, *imagenet, 99)
+        gen_resample("resample_down24.npz", 4, (75, 100), 24, False, *imagenet, 5)
+    if a.only_resample:
+        sys.exit(0)
     if not a.only_ddp:
         # CIFAR recipe (04_accelerate/01_cifar_accelerate.ipynb:295-298) and the crop-without-padding
         # ImageNet-style recipe (02_deepspeed/03_1k_imagenet_deepspeed_resnet.py:45-53) at fixture size
