@@ -342,10 +342,10 @@ def main():
 
     for _ in range(args.warmup):
         step(dev_u8, dev_y)
-    _lib.CALLS.clear()
+    _lib.reset_calls()
     with ClockSampler(local_rank) as clocks:
         ms_dev = timed(lambda: step(dev_u8, dev_y), args.steps)
-    launches = sum(n * _lib.LAUNCHES_PER_CALL.get(k, 1) for k, n in _lib.CALLS.items())
+    launches = sum(n * _lib.LAUNCHES_PER_CALL.get(k, 1) for k, n in _lib.total_calls().items())
     loss_dev = float(step(dev_u8, dev_y).detach())
 
     # End to end through the public API: every step's source batch starts in pinned HOST memory

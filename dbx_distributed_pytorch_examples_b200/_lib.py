@@ -54,6 +54,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         newest = max(os.path.getmtime(p) for p in srcs + hdrs if os.path.exists(p))
         if os.path.getmtime(LIB_PATH) >= newest:
             build_fastcall()
+            build_autograd()
             return LIB_PATH
     nvcc = os.environ.get("NVCC", "nvcc")
     cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_PATH] + srcs
@@ -63,6 +64,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if verbose:
         print(proc.stderr)
     build_fastcall(force=True)
+    build_autograd(force=True)
     return LIB_PATH
 
 
@@ -83,6 +85,36 @@ def build_fastcall(force: bool = False) -> str:
     proc = subprocess.run(cmd, capture_output=True, text=True, stdin=subprocess.DEVNULL, timeout=300)
     if proc.returncode != 0:
         raise B200DPError("gcc failed on fastcall.c:\n" + proc.stdout + proc.stderr)
+    return out
+
+
+def _autograd_path() -> str:
+    import sysconfig
+
+    return os.path.join(PKG_DIR, "_b200dp_autograd" + sysconfig.get_config_var("EXT_SUFFIX"))
+
+
+def build_autograd(force: bool = False) -> str:
+    """g++-compile csrc/autograd_bn.cpp (the SyncBN autograd node as a C++ torch::autograd::Function,
+    host plumbing over the same C ABI) against the installed torch headers, in-tree."""
+    import sysconfig
+
+    import torch
+    from torch.utils import cpp_extension
+
+    src, out = os.path.join(CSRC_DIR, "autograd_bn.cpp"), _autograd_path()
+    if not force and os.path.exists(out) and os.path.getmtime(out) >= os.path.getmtime(src):
+        return out
+    inc = cpp_extension.include_paths() + [sysconfig.get_paths()["include"],
+                                           os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "include")]
+    libdir = os.path.join(os.path.dirname(torch.__file__), "lib")
+    cmd = ([os.environ.get("CXX", "g++"), "-O2", "-std=c++17", "-shared", "-fPIC", "-DTORCH_EXTENSION_NAME=_b200dp_autograd",
+            f"-D_GLIBCXX_USE_CXX11_ABI={int(torch._C._GLIBCXX_USE_CXX11_ABI)}"] + [f"-I{i}" for i in inc] +
+           [src, "-o", out, f"-L{libdir}", "-lc10", "-lc10_cuda", "-ltorch_cpu", "-ltorch_cuda", "-ltorch",
+            "-ltorch_python", f"-Wl,-rpath,{libdir}", "-ldl"])
+    proc = subprocess.run(cmd, capture_output=True, text=True, stdin=subprocess.DEVNULL, timeout=1800)
+    if proc.returncode != 0:
+        raise B200DPError("g++ failed on autograd_bn.cpp:\n" + proc.stdout + proc.stderr)
     return out
 
 
@@ -212,6 +244,51 @@ def fast():
                      ctypes.cast(cdll.b200dp_bn_backward, c_void_p).value)
             _fast = mod
     return _fast or None
+
+
+_native = None
+
+
+def native():
+    """The C++ autograd node module bound to the loaded library, or None when it has not been built
+    (the python autograd.Function in syncbn.py then drives the same two C-ABI calls).
+    B200DP_PY_AUTOGRAD=1 forces the python node."""
+    global _native
+    if _native is None:
+        path = _autograd_path()
+        if not os.path.exists(path) or os.environ.get("B200DP_PY_AUTOGRAD", "0") == "1":
+            _native = False
+        else:
+            import importlib.util
+
+            import torch  # noqa: F401  (the extension links against libtorch)
+
+            lib()  # the ctypes handle first: both must refer to the same loaded library
+            spec = importlib.util.spec_from_file_location("_b200dp_autograd", path)
+            mod = importlib.util.module_from_spec(spec)
+            spec.loader.exec_module(mod)
+            mod.bind(LIB_PATH)
+            _native = mod
+    return _native or None
+
+
+def total_calls() -> dict:
+    """CALLS plus the calls the C++ autograd node made (it does not go through _Entry)."""
+    out = dict(CALLS)
+    if _native:
+        f, b = _native.counters()
+        out["b200dp_bn_forward"] = out.get("b200dp_bn_forward", 0) + f - _native_base[0]
+        out["b200dp_bn_backward"] = out.get("b200dp_bn_backward", 0) + b - _native_base[1]
+    return out
+
+
+_native_base = [0, 0]
+
+
+def reset_calls() -> None:
+    CALLS.clear()
+    if _native:
+        _native_base[0], _native_base[1] = _native.counters()
 
 
 def check(rc: int, what: str = "") -> None:

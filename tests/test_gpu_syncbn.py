@@ -153,3 +153,48 @@ def test_linearity_and_large_layer_property():
     y.backward(torch.randn_like(y))
     s = xr.grad.float().sum((0, 2, 3))
     assert float(s.abs().max()) < 0.05 * float(xr.grad.float().abs().sum((0, 2, 3)).max())
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("mode", ["plain", "relu", "addrelu"])
+def test_cpp_autograd_node_equals_python_node(monkeypatch, dtype, mode):
+    """csrc/autograd_bn.cpp is host plumbing over the same two C-ABI calls: identical bits, identical
+    side effects (running statistics, counters), identical errors."""
+    from dbx_distributed_pytorch_examples_b200 import _lib
+    assert _lib.native() is not None, "the C++ autograd node was not built"
+    torch.manual_seed(5)
+    shape = (5, 96, 7, 9)
+    mk = lambda: torch.randn(shape, device="cuda").to(dtype).contiguous(memory_format=torch.channels_last)  # noqa: E731
+    x, dy = mk(), mk()
+    res = mk() if mode == "addrelu" else None
+    w, b = torch.rand(96, device="cuda") + 0.5, torch.randn(96, device="cuda")
+    rm, rv = torch.randn(96, device="cuda"), torch.rand(96, device="cuda") + 0.5
+    outs = []
+    for use_cpp in (True, False):
+        if not use_cpp:
+            monkeypatch.setattr(_lib, "_native", False)
+        before = _lib.total_calls().get("b200dp_bn_forward", 0)
+        bn, y, dx, dres = run_ours(x, res, dy, w, b, rm, rv, mode != "plain")
+        assert _lib.total_calls().get("b200dp_bn_forward", 0) == before + 1
+        outs.append((y, dx, dres, bn.weight.grad.clone(), bn.bias.grad.clone(), bn.running_mean.clone(),
+                     bn.running_var.clone(), bn.num_batches_tracked.clone()))
+    for a, c in zip(*outs):
+        assert (a is None and c is None) or torch.equal(a, c)
+
+
+def test_cpp_autograd_node_errors_and_frozen_inputs():
+    bn = b200.B200SyncBatchNorm(4).cuda()
+    with pytest.raises(ValueError, match="more than 1 value per channel"):
+        bn(torch.randn(1, 4, 1, 1, device="cuda"))
+    with pytest.raises(ValueError, match="residual must have the shape"):
+        bn(torch.randn(2, 4, 3, 3, device="cuda"), torch.randn(2, 4, 3, 2, device="cuda"))
+    # input without grad, affine frozen: the backward still runs and returns nothing for them
+    bn.weight.requires_grad_(False)
+    x = torch.randn(2, 4, 3, 3, device="cuda")
+    r = torch.randn(2, 4, 3, 3, device="cuda", requires_grad=True)
+    bn(x, r).sum().backward()
+    assert bn.weight.grad is None and bn.bias.grad is not None and r.grad is not None
+    # NCHW-contiguous and 2D inputs go through the same node
+    y = bn(torch.randn(2, 4, 3, 3, device="cuda").contiguous())
+    assert y.shape == (2, 4, 3, 3)
+    assert b200.B200SyncBatchNorm(4).cuda()(torch.randn(6, 4, device="cuda")).shape == (6, 4)

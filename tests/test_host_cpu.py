@@ -187,3 +187,15 @@ def test_workload_matches_reference_model():
     assert list(sa) == list(sb) and all(torch.equal(sa[k], sb[k]) for k in sa)
     x = torch.randn(4, 3, 32, 32)
     assert torch.equal(ours(x), ref(x))
+
+
+def test_autograd_extension_loads_and_binds():
+    """csrc/autograd_bn.cpp builds in-tree and resolves the SyncBN entry points of the C ABI."""
+    nat = _lib.native()
+    assert nat is not None, "build it with __graft_entry__.build()"
+    assert nat.counters() == (0, 0) or all(v >= 0 for v in nat.counters())
+    for name in ("bind", "fused_syncbn", "counters"):
+        assert callable(getattr(nat, name))
+    with pytest.raises(RuntimeError, match="cannot load"):
+        nat.bind("/nonexistent/libb200dp.so")
+    nat.bind(_lib.LIB_PATH)
