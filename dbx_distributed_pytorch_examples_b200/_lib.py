@@ -81,7 +81,7 @@ def build_fastcall(force: bool = False) -> str:
     src, out = os.path.join(CSRC_DIR, "fastcall.c"), _fast_path()
     if not force and os.path.exists(out) and os.path.getmtime(out) >= os.path.getmtime(src):
         return out
-    cmd = [os.environ.get("CC", "gcc"), "-O2", "-shared", "-fPIC", "-I" + sysconfig.get_paths()["include"], "-o", out, src]
+    cmd = [os.environ.get("B200DP_CC", "gcc"), "-O2", "-shared", "-fPIC", "-I" + sysconfig.get_paths()["include"], "-o", out, src]
     proc = subprocess.run(cmd, capture_output=True, text=True, stdin=subprocess.DEVNULL, timeout=300)
     if proc.returncode != 0:
         raise B200DPError("gcc failed on fastcall.c:\n" + proc.stdout + proc.stderr)
@@ -108,7 +108,9 @@ def build_autograd(force: bool = False) -> str:
     inc = cpp_extension.include_paths() + [sysconfig.get_paths()["include"],
                                            os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "include")]
     libdir = os.path.join(os.path.dirname(torch.__file__), "lib")
-    cmd = ([os.environ.get("CXX", "g++"), "-O2", "-std=c++17", "-shared", "-fPIC", "-DTORCH_EXTENSION_NAME=_b200dp_autograd",
+    # the distribution's g++ (the one whose libstdc++ the torch wheel runs against here), not $CXX: an
+    # extension built by a toolchain with its own libstdc++ crashed on its first formatted exception
+    cmd = ([os.environ.get("B200DP_CXX", "g++"), "-O2", "-std=c++17", "-shared", "-fPIC", "-DTORCH_EXTENSION_NAME=_b200dp_autograd",
             f"-D_GLIBCXX_USE_CXX11_ABI={int(torch._C._GLIBCXX_USE_CXX11_ABI)}"] + [f"-I{i}" for i in inc] +
            [src, "-o", out, f"-L{libdir}", "-lc10", "-lc10_cuda", "-ltorch_cpu", "-ltorch_cuda", "-ltorch",
             "-ltorch_python", f"-Wl,-rpath,{libdir}", "-ldl"])

@@ -23,6 +23,7 @@
 // residual); bwd reduce 4 B; bwd apply 6 B (+2 for d_residual); the ReLU mask
 // is recomputed from x (mode 1) or read from y (mode 2, +2 B per bwd pass).
 #include <mutex>
+#include <stdlib.h>
 
 #include <cooperative_groups.h>
 
@@ -478,11 +479,12 @@ struct is_bf16<__nv_bfloat16> { static constexpr bool value = true; };
 
 // =============================== forward: stats ===============================
 constexpr int kDepthStats = 8;
+constexpr int kDefaultBnOrder = 10;  // the apply kernels walk against the reductions (B200: -1 % step time)
 
 template <typename T>
 __global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kT, kOccFwd)
 bn_stats_kernel(const T* __restrict__ x, int64_t M, int C, void* scratch, float* stats_local,
-                b200dp_peers P, uint32_t seq) {
+                b200dp_peers P, uint32_t seq, int rev) {
   constexpr int N = Vec<T>::N;
   using Ring = RowRing<kDepthStats, 1, false>;
   constexpr int kTreeBytes = (2 * N * kT + kT) * 4;
@@ -501,8 +503,9 @@ bn_stats_kernel(const T* __restrict__ x, int64_t M, int C, void* scratch, float*
 
   if (chan_ok) {
     const RowRange rr = my_rows(M, r);
-    const T* base = x + rr.first * C + c0;
-    const int64_t step = rr.step * C;
+    // rev: walk this thread's rows from the last to the first (see bn_order())
+    const int64_t step = rev ? -rr.step * C : rr.step * C;
+    const T* base = x + rr.first * C + c0 + (rev ? (int64_t)(rr.count - 1) * rr.step * C : 0);
     auto ptrs = [&](int k, const void*& p0, const void*& p1, const void*& p2) {
       p0 = base + k * step;
       p1 = p2 = nullptr;
@@ -586,6 +589,7 @@ struct FwdArgs {
   const float* given_var;
   // optional output: one 32-bit word per 16-byte vector of y, bit j = (y[j] > 0)
   uint32_t* maskw;
+  int rev;  // walk the rows from the last to the first
 };
 
 // Per-channel coefficients of one chunk are worked out once per CTA, by its first kCV
@@ -611,7 +615,8 @@ __global__ void __launch_bounds__(kT, kOccFwd) bn_fwd_apply_kernel(FwdArgs A, b2
   const T* rb = static_cast<const T*>(A.res);
   T* yb = static_cast<T*>(A.y);
   const RowRange rr = my_rows(A.M, r);
-  const int64_t off0 = rr.first * C + c0, step = rr.step * C;
+  const int64_t step = A.rev ? -rr.step * C : rr.step * C;
+  const int64_t off0 = rr.first * C + c0 + (A.rev ? (int64_t)(rr.count - 1) * rr.step * C : 0);
   auto ptrs = [&](int k, const void*& p0, const void*& p1, const void*& p2) {
     p0 = xb + off0 + k * step;
     p1 = RES ? (const void*)(rb + off0 + k * step) : nullptr;
@@ -733,7 +738,7 @@ __global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kT, kOccFwd)
 bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T* __restrict__ yo,
                      int64_t M, int C, const float* save_mean, const float* save_invstd,
                      const float* weight, const float* bias, void* scratch, float* sums_local,
-                     float* grad_weight, float* grad_bias, b200dp_peers P, uint32_t seq) {
+                     float* grad_weight, float* grad_bias, b200dp_peers P, uint32_t seq, int rev) {
   constexpr int N = Vec<T>::N;
   using Ring = RowRing<RELU >= 2 ? 3 : 4, RELU >= 2 ? 3 : 2, false, RELU == 3>;  // 32 or 36 KiB (static smem limit 48 KiB)
   constexpr int kTreeBytes = 2 * N * kT * 4;
@@ -750,7 +755,8 @@ bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T*
   for (int k = 0; k < N; ++k) s1[k] = s2[k] = 0.f;
   if (chan_ok) {
     const RowRange rr = my_rows(M, r);
-    const int64_t off0 = rr.first * C + c0, step = rr.step * C;
+    const int64_t step = rev ? -rr.step * C : rr.step * C;
+    const int64_t off0 = rr.first * C + c0 + (rev ? (int64_t)(rr.count - 1) * rr.step * C : 0);
     auto ptrs = [&](int k, const void*& p0, const void*& p1, const void*& p2) {
       p0 = dy + off0 + k * step;
       p1 = x + off0 + k * step;
@@ -856,6 +862,7 @@ struct BwdArgs {
   const float* bias;
   const float* sums_local;
   const float* save_count;
+  int rev;
 };
 
 template <typename T, int RELU, bool DRES>
@@ -875,7 +882,8 @@ __global__ void __launch_bounds__(kT, kOccBwd) bn_bwd_apply_kernel(BwdArgs A, b2
   T* dxb = static_cast<T*>(A.dx);
   T* dresb = static_cast<T*>(A.dres);
   const RowRange rr = my_rows(A.M, r);
-  const int64_t off0 = rr.first * C + c0, step = rr.step * C;
+  const int64_t step = A.rev ? -rr.step * C : rr.step * C;
+  const int64_t off0 = rr.first * C + c0 + (A.rev ? (int64_t)(rr.count - 1) * rr.step * C : 0);
   auto ptrs = [&](int k, const void*& p0, const void*& p1, const void*& p2) {
     p0 = dyb + off0 + k * step;
     p1 = xb + off0 + k * step;
@@ -987,6 +995,19 @@ __global__ void __launch_bounds__(kT, kOccBwd) bn_bwd_apply_kernel(BwdArgs A, b2
   ring.run(nrows, ptrs, proc);
 }
 
+// Row traversal order of the four training kernels: bit 0 statistics, bit 1 forward apply,
+// bit 2 backward reduce, bit 3 backward apply; a set bit walks the rows from the last to the
+// first.  A kernel that runs against the direction of the one before it starts on the rows
+// that kernel touched last, which are the ones still in L2 (126 MB of it on B200).
+// B200DP_BN_ORDER overrides the default (read once).
+int bn_order() {
+  static const int order = [] {
+    const char* e = getenv("B200DP_BN_ORDER");
+    return e && e[0] ? atoi(e) : kDefaultBnOrder;
+  }();
+  return order;
+}
+
 // Launch with (or without) the programmatic-stream-serialization attribute.
 thread_local bool t_pdl_next = false;  // set by b200dp_bn_forward / _backward around their second launch
 
@@ -1043,11 +1064,11 @@ extern "C" int b200dp_bn_fwd_stats(const void* x, int dtype, int64_t M, int C, v
   if (dtype == B200DP_BF16) {
     const Grid2 g = plan_grid_clustered<__nv_bfloat16>(M, C, max_active_clusters(bn_stats_kernel<__nv_bfloat16>));
     bn_stats_kernel<__nv_bfloat16><<<dim3(g.gx, g.gy), kT, 0, s>>>(
-        static_cast<const __nv_bfloat16*>(x), M, C, scratch, stats_local, P, seq);
+        static_cast<const __nv_bfloat16*>(x), M, C, scratch, stats_local, P, seq, bn_order() & 1);
   } else {
     const Grid2 g = plan_grid_clustered<float>(M, C, max_active_clusters(bn_stats_kernel<float>));
     bn_stats_kernel<float><<<dim3(g.gx, g.gy), kT, 0, s>>>(static_cast<const float*>(x), M, C,
-                                                           scratch, stats_local, P, seq);
+                                                           scratch, stats_local, P, seq, bn_order() & 1);
   }
   B200DP_LAUNCH_CHECK();
   return B200DP_OK;
@@ -1107,12 +1128,12 @@ extern "C" int b200dp_bn_fwd_stats_noalloc(const void* x, int dtype, int64_t M, 
     g = plan_grid_clustered<__nv_bfloat16>(M, C, max_active_clusters(bn_stats_kernel<__nv_bfloat16>));
     if ((size_t)g.gx * g.gy * kCV * Vec<__nv_bfloat16>::N > (size_t)kMaxPartials) return B200DP_ETOOBIG;
     bn_stats_kernel<__nv_bfloat16><<<dim3(g.gx, g.gy), kT, 0, s>>>(
-        static_cast<const __nv_bfloat16*>(x), M, C, scratch, stats_local, P, 0);
+        static_cast<const __nv_bfloat16*>(x), M, C, scratch, stats_local, P, 0, 0);
   } else {
     g = plan_grid_clustered<float>(M, C, max_active_clusters(bn_stats_kernel<float>));
     if ((size_t)g.gx * g.gy * kCV * Vec<float>::N > (size_t)kMaxPartials) return B200DP_ETOOBIG;
     bn_stats_kernel<float><<<dim3(g.gx, g.gy), kT, 0, s>>>(static_cast<const float*>(x), M, C,
-                                                           scratch, stats_local, P, 0);
+                                                           scratch, stats_local, P, 0, 0);
   }
   B200DP_LAUNCH_CHECK();
   return B200DP_OK;
@@ -1151,7 +1172,7 @@ extern "C" int b200dp_bn_fwd_apply(const void* x, const void* residual, void* y,
   if (M > 0 && !y) return B200DP_EINVAL;
   if ((rc = check_comm(comm, seq))) return rc;
   FwdArgs A{x, residual, y, M, C, stats_local, weight, bias, eps, momentum, running_mean,
-            running_var, save_mean, save_invstd, save_count, nullptr, nullptr, relu_mask};
+            running_var, save_mean, save_invstd, save_count, nullptr, nullptr, relu_mask, (bn_order() >> 1) & 1};
   const b200dp_peers P = b200dp_make_peers(comm);
   cudaStream_t s = (cudaStream_t)stream;
   return dtype == B200DP_BF16 ? launch_fwd_apply<__nv_bfloat16>(A, relu != 0, P, seq, s)
@@ -1169,7 +1190,7 @@ extern "C" int b200dp_bn_inference(const void* x, const void* residual, void* y,
   if (M == 0) return B200DP_OK;
   if (!y) return B200DP_EINVAL;
   FwdArgs A{x, residual, y, M, C, nullptr, weight, bias, eps, 0.f, nullptr, nullptr, nullptr,
-            nullptr, nullptr, running_mean, running_var, nullptr};
+            nullptr, nullptr, running_mean, running_var, nullptr, 0};
   const b200dp_peers P = b200dp_make_peers(nullptr);
   cudaStream_t s = (cudaStream_t)stream;
   return dtype == B200DP_BF16 ? launch_fwd_apply<__nv_bfloat16>(A, relu != 0, P, 0, s)
@@ -1195,7 +1216,7 @@ int launch_bwd_reduce(const void* dy, const void* x, const void* yo, int64_t M, 
 #define B200DP_BWD_REDUCE(R)                                                                   \
   bn_bwd_reduce_kernel<T, R><<<grid, kT, 0, s>>>(pdy, px, py, M, C, save_mean, save_invstd,    \
                                                  weight, bias, scratch, sums_local,            \
-                                                 grad_weight, grad_bias, P, seq)
+                                                 grad_weight, grad_bias, P, seq, (bn_order() >> 2) & 1)
   if (relu == 0) B200DP_BWD_REDUCE(0);
   else if (relu == 1) B200DP_BWD_REDUCE(1);
   else if (relu == 2) B200DP_BWD_REDUCE(2);
@@ -1268,7 +1289,7 @@ extern "C" int b200dp_bn_bwd_apply(const void* dy, const void* x, const void* y_
   if (!save_mean || !save_invstd || !sums_local || !save_count) return B200DP_EINVAL;
   if ((rc = check_comm(comm, seq))) return rc;
   BwdArgs A{dy, x, y_out, dx, d_residual, M, C, save_mean, save_invstd, weight, bias,
-            sums_local, save_count};
+            sums_local, save_count, (bn_order() >> 3) & 1};
   const b200dp_peers P = b200dp_make_peers(comm);
   cudaStream_t s = (cudaStream_t)stream;
   return dtype == B200DP_BF16 ? launch_bwd_apply<__nv_bfloat16>(A, relu, P, seq, s)
