@@ -81,6 +81,61 @@ __device__ __forceinline__ int clip8(int acc) {
   return min(max(acc >> kPrecisionBits, 0), 255);
 }
 
+// Horizontal pass of one output column over the tile's source rows r0, r0+rstep, …, with the
+// column's TAPS coefficients and byte offsets in registers.  Coefficients past xmax are zero
+// (coeffs_for pads them) and read the column's first pixel again, which is always inside the box.
+// No clip: the weights are non-negative and sum to 2^22 (+ at most a few units of rounding), so
+// 2^21 + sum(p*k) < 256 * 2^22 and the shift alone yields 0..255, as Pillow's clip8 would.
+template <int TAPS>
+__device__ __forceinline__ void hpass_column(const uint8_t* __restrict__ img, int row_stride, int nrows, int r0,
+                                             int rstep, const int32_t* k, int xmin, int xmax, uint8_t* tcol,
+                                             int pitch) {
+  int kk[TAPS];
+  int off[TAPS];
+#pragma unroll
+  for (int x = 0; x < TAPS; ++x) {
+    kk[x] = k[x];
+    off[x] = (xmin + (x < xmax ? x : 0)) * 3;
+  }
+  const uint8_t* row = img + (size_t)r0 * row_stride;
+  uint8_t* t = tcol + r0 * pitch;
+  for (int r = r0; r < nrows; r += rstep) {
+    int s0 = 1 << (kPrecisionBits - 1), s1 = s0, s2 = s0;
+#pragma unroll
+    for (int x = 0; x < TAPS; ++x) {
+      const uint8_t* px = row + off[x];
+      s0 += (int)__ldg(px) * kk[x];
+      s1 += (int)__ldg(px + 1) * kk[x];
+      s2 += (int)__ldg(px + 2) * kk[x];
+    }
+    t[0] = (uint8_t)(s0 >> kPrecisionBits);
+    t[1] = (uint8_t)(s1 >> kPrecisionBits);
+    t[2] = (uint8_t)(s2 >> kPrecisionBits);
+    row += (size_t)rstep * row_stride;
+    t += rstep * pitch;
+  }
+}
+
+// Any number of taps, coefficients read from shared memory (down-scaling by more than 2.5x).
+__device__ __forceinline__ void hpass_column_any(const uint8_t* __restrict__ img, int row_stride, int nrows, int r0,
+                                                 int rstep, const int32_t* k, int xmin, int xmax, uint8_t* tcol,
+                                                 int pitch) {
+  for (int r = r0; r < nrows; r += rstep) {
+    const uint8_t* px = img + (size_t)r * row_stride + xmin * 3;
+    int s0 = 1 << (kPrecisionBits - 1), s1 = s0, s2 = s0;
+    for (int x = 0; x < xmax; ++x) {
+      const int kx = k[x];
+      s0 += (int)__ldg(px + 3 * x) * kx;
+      s1 += (int)__ldg(px + 3 * x + 1) * kx;
+      s2 += (int)__ldg(px + 3 * x + 2) * kx;
+    }
+    uint8_t* t = tcol + r * pitch;
+    t[0] = (uint8_t)clip8(s0);
+    t[1] = (uint8_t)clip8(s1);
+    t[2] = (uint8_t)clip8(s2);
+  }
+}
+
 template <bool VEC>
 __global__ void __launch_bounds__(kThreads) resample_kernel(const ResampleArgs a) {
   extern __shared__ __align__(16) uint8_t smem[];
@@ -91,20 +146,26 @@ __global__ void __launch_bounds__(kThreads) resample_kernel(const ResampleArgs a
   int* bnd_h = coef_v + a.tile_rows * a.kv;
   int* bnd_v = bnd_h + 2 * a.W;
   uint16_t* lut = reinterpret_cast<uint16_t*>(bnd_v + 2 * a.tile_rows);
+  __shared__ int s_taps_h;
 
   const int b = blockIdx.y;
   const int y0 = blockIdx.x * a.tile_rows;
   const int rows = min(a.tile_rows, a.H - y0);
   const int tid = threadIdx.x;
+  if (tid == 0) s_taps_h = 0;
 
   // the crop box, forced inside the slab (torchvision never produces anything else)
   const int32_t* p = a.params + (size_t)b * 5;
   int bh = min(max(p[2], 1), a.Hs), bw = min(max(p[3], 1), a.Ws);
   const int bi = min(max(p[0], 0), a.Hs - bh), bj = min(max(p[1], 0), a.Ws - bw);
   const bool flip = p[4] != 0;
+  __syncthreads();
 
-  for (int c = tid; c < a.W; c += kThreads)
+  int my_taps = 0;
+  for (int c = tid; c < a.W; c += kThreads) {
     coeffs_for(c, bw, a.W, a.kh, coef_h + c * a.kh, &bnd_h[2 * c], &bnd_h[2 * c + 1]);
+    my_taps = max(my_taps, bnd_h[2 * c + 1]);
+  }
   for (int y = tid; y < rows; y += kThreads)
     coeffs_for(y0 + y, bh, a.H, a.kv, coef_v + y * a.kv, &bnd_v[2 * y], &bnd_v[2 * y + 1]);
   for (int e = tid; e < 768; e += kThreads) {
@@ -113,73 +174,82 @@ __global__ void __launch_bounds__(kThreads) resample_kernel(const ResampleArgs a
     const float y = __fdiv_rn(__fsub_rn(x, a.mean[c]), a.std[c]);         // Normalize: sub_(mean).div_(std)
     lut[e] = __bfloat16_as_ushort(__float2bfloat16_rn(y));
   }
+  my_taps = __reduce_max_sync(0xffffffffu, my_taps);
+  if ((tid & 31) == 0 && my_taps) atomicMax(&s_taps_h, my_taps);
   __syncthreads();
 
   // ---- horizontal pass over the source rows this tile's vertical pass touches --------------
+  // A thread owns one output column (and every rgroups-th row when the image is narrow).
   const int first = bnd_v[0];
   int nrows = bnd_v[2 * (rows - 1)] + bnd_v[2 * (rows - 1) + 1] - first;
   nrows = min(nrows, a.temp_rows);
   const uint8_t* img = a.src + ((size_t)b * a.Hs + (bi + first)) * a.Ws * 3 + (size_t)bj * 3;
-  const int items = nrows * a.W;
-  for (int it = tid; it < items; it += kThreads) {
-    const int r = it / a.W, c = it - r * a.W;
-    const int xmin = bnd_h[2 * c], xmax = bnd_h[2 * c + 1];
-    const int32_t* k = coef_h + c * a.kh;
-    const uint8_t* px = img + (size_t)r * a.Ws * 3 + xmin * 3;
-    int s0 = 1 << (kPrecisionBits - 1), s1 = s0, s2 = s0;
-    for (int x = 0; x < xmax; ++x) {
-      const int kx = k[x];
-      s0 += (int)__ldg(px + 3 * x) * kx;
-      s1 += (int)__ldg(px + 3 * x + 1) * kx;
-      s2 += (int)__ldg(px + 3 * x + 2) * kx;
+  {
+    const int cw = min((a.W + 31) & ~31, kThreads);  // columns per pass, whole warps
+    const int rgroups = kThreads / cw, rg = tid / cw;
+    const int taps = s_taps_h, row_stride = a.Ws * 3;
+    if (rg < rgroups) {
+      for (int c = tid - rg * cw; c < a.W; c += cw) {
+        const int xmin = bnd_h[2 * c], xmax = bnd_h[2 * c + 1];
+        const int32_t* k = coef_h + c * a.kh;
+        uint8_t* tcol = temp + (flip ? a.W - 1 - c : c) * 3;
+        if (taps <= 3) hpass_column<3>(img, row_stride, nrows, rg, rgroups, k, xmin, xmax, tcol, a.pitch);
+        else if (taps == 4) hpass_column<4>(img, row_stride, nrows, rg, rgroups, k, xmin, xmax, tcol, a.pitch);
+        else if (taps == 5) hpass_column<5>(img, row_stride, nrows, rg, rgroups, k, xmin, xmax, tcol, a.pitch);
+        else hpass_column_any(img, row_stride, nrows, rg, rgroups, k, xmin, xmax, tcol, a.pitch);
+      }
     }
-    uint8_t* t = temp + (size_t)r * a.pitch + (flip ? a.W - 1 - c : c) * 3;
-    t[0] = (uint8_t)clip8(s0);
-    t[1] = (uint8_t)clip8(s1);
-    t[2] = (uint8_t)clip8(s2);
   }
   __syncthreads();
 
   // ---- vertical pass + normalisation ---------------------------------------------------------
+  // A thread owns one group of 8 consecutive bytes of the row (and every vslots-th output row).
   const int row_elems = a.W * 3;
   const int groups = (row_elems + 7) >> 3;
-  const int vitems = rows * groups;
-  for (int it = tid; it < vitems; it += kThreads) {
-    const int y = it / groups, g = it - y * groups;
-    const int ymin = bnd_v[2 * y] - first, ymax = bnd_v[2 * y + 1];
-    const int32_t* k = coef_v + y * a.kv;
-    int acc[8];
+  const int gw = min(groups, kThreads);
+  const int vslots = kThreads / gw, vs = tid / gw;
+  if (vs < vslots) {
+    for (int g = tid - vs * gw; g < groups; g += gw) {
+      // channel of element e of this group is (2g + e) % 3: three table bases per thread
+      const int ch0 = (2 * g) % 3;
+      const uint16_t* lt0 = lut + ch0 * 256;
+      const uint16_t* lt1 = lut + (ch0 == 2 ? 0 : ch0 + 1) * 256;
+      const uint16_t* lt2 = lut + (ch0 == 0 ? 2 : ch0 - 1) * 256;
+      for (int y = vs; y < rows; y += vslots) {
+        const int ymin = bnd_v[2 * y] - first, ymax = bnd_v[2 * y + 1];
+        const int32_t* k = coef_v + y * a.kv;
+        int acc[8];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) acc[e] = 1 << (kPrecisionBits - 1);
-    const uint8_t* col = temp + (size_t)ymin * a.pitch + g * 8;
-    for (int x = 0; x < ymax; ++x) {
-      const uint2 v = *reinterpret_cast<const uint2*>(col + (size_t)x * a.pitch);
-      const int kx = k[x];
+        for (int e = 0; e < 8; ++e) acc[e] = 1 << (kPrecisionBits - 1);
+        const uint8_t* col = temp + ymin * a.pitch + g * 8;
+        for (int x = 0; x < ymax; ++x) {
+          const uint2 v = *reinterpret_cast<const uint2*>(col + x * a.pitch);
+          const int kx = k[x];
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        acc[e] += (int)((v.x >> (8 * e)) & 255u) * kx;
-        acc[4 + e] += (int)((v.y >> (8 * e)) & 255u) * kx;
+          for (int e = 0; e < 4; ++e) {
+            acc[e] += (int)__byte_perm(v.x, 0, 0x4440 | e) * kx;
+            acc[4 + e] += (int)__byte_perm(v.y, 0, 0x4440 | e) * kx;
+          }
+        }
+        uint32_t o[8];
+        // no clip, as in the horizontal pass: the shift alone yields 0..255
+        o[0] = lt0[acc[0] >> kPrecisionBits]; o[1] = lt1[acc[1] >> kPrecisionBits]; o[2] = lt2[acc[2] >> kPrecisionBits];
+        o[3] = lt0[acc[3] >> kPrecisionBits]; o[4] = lt1[acc[4] >> kPrecisionBits]; o[5] = lt2[acc[5] >> kPrecisionBits];
+        o[6] = lt0[acc[6] >> kPrecisionBits]; o[7] = lt1[acc[7] >> kPrecisionBits];
+        uint16_t* out = a.dst + ((size_t)b * a.H + (y0 + y)) * row_elems + g * 8;
+        if (VEC) {
+          uint4 w;
+          w.x = o[0] | (o[1] << 16);
+          w.y = o[2] | (o[3] << 16);
+          w.z = o[4] | (o[5] << 16);
+          w.w = o[6] | (o[7] << 16);
+          *reinterpret_cast<uint4*>(out) = w;
+        } else {
+#pragma unroll
+          for (int e = 0; e < 8; ++e)
+            if (g * 8 + e < row_elems) out[e] = (uint16_t)o[e];
+        }
       }
-    }
-    int ch = (g * 8) % 3;
-    uint16_t o[8];
-#pragma unroll
-    for (int e = 0; e < 8; ++e) {
-      o[e] = lut[ch * 256 + clip8(acc[e])];
-      ch = ch == 2 ? 0 : ch + 1;
-    }
-    uint16_t* out = a.dst + ((size_t)b * a.H + (y0 + y)) * row_elems + g * 8;
-    if (VEC) {
-      uint4 w;
-      w.x = o[0] | ((uint32_t)o[1] << 16);
-      w.y = o[2] | ((uint32_t)o[3] << 16);
-      w.z = o[4] | ((uint32_t)o[5] << 16);
-      w.w = o[6] | ((uint32_t)o[7] << 16);
-      *reinterpret_cast<uint4*>(out) = w;
-    } else {
-#pragma unroll
-      for (int e = 0; e < 8; ++e)
-        if (g * 8 + e < row_elems) out[e] = o[e];
     }
   }
 }
