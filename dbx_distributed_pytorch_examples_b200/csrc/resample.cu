@@ -137,7 +137,7 @@ __device__ __forceinline__ void hpass_column_any(const uint8_t* __restrict__ img
 }
 
 template <bool VEC>
-__global__ void __launch_bounds__(kThreads) resample_kernel(const ResampleArgs a) {
+__global__ void __launch_bounds__(kThreads, 5) resample_kernel(const ResampleArgs a) {
   extern __shared__ __align__(16) uint8_t smem[];
   // layout: temp [R][pitch] | kh coef [W][kh] | kv coef [T][kv] | bounds h [W][2] | bounds v [T][2] | lut [3][256]
   uint8_t* temp = smem;
@@ -302,6 +302,7 @@ extern "C" int b200dp_resized_crop_u8_bf16(const uint8_t* src, int B, int Hs, in
   const bool vec = (W * 3) % 8 == 0;
   auto kern = vec ? resample_kernel<true> : resample_kernel<false>;
   B200DP_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBudget));
+  B200DP_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
   dim3 grid((H + T - 1) / T, B);
   kern<<<grid, kThreads, smem, (cudaStream_t)stream>>>(a);
   B200DP_LAUNCH_CHECK();
