@@ -22,11 +22,12 @@ from .distributor import DeepspeedTorchDistributor, TorchDistributor  # noqa: F4
 from .feed import DeviceFeeder, LossReader, PinnedImageDataset, ShardedBatchSampler  # noqa: F401
 from .fusion import fuse_bn_relu  # noqa: F401
 from .syncbn import B200SyncBatchNorm, convert_sync_batchnorm  # noqa: F401
+from .pool import B200MaxPool2d  # noqa: F401
 from .transform import (BatchTransform, ResizeBatchTransform, draw_crop_flip_params,  # noqa: F401
                         draw_resized_crop_flip_params)
 
 __all__ = [
     "B200DDP", "prepare_model", "B200SyncBatchNorm", "BatchTransform", "Communicator", "TorchDistributor",
-    "DeepspeedTorchDistributor", "convert_sync_batchnorm", "fuse_bn_relu", "draw_crop_flip_params", "ResizeBatchTransform", "draw_resized_crop_flip_params",
+    "DeepspeedTorchDistributor", "convert_sync_batchnorm", "fuse_bn_relu", "draw_crop_flip_params", "B200MaxPool2d", "ResizeBatchTransform", "draw_resized_crop_flip_params",
     "B200DPError", "build", "DeviceFeeder", "LossReader", "PinnedImageDataset", "ShardedBatchSampler",
 ]

@@ -15,7 +15,7 @@ from ctypes import POINTER, Structure, c_char_p, c_float, c_int, c_int32, c_int6
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC_DIR = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "libb200dp.so")
-SOURCES = ["augment.cu", "resample.cu", "bn.cu", "comm.cu", "update.cu"]
+SOURCES = ["augment.cu", "resample.cu", "bn.cu", "pool.cu", "comm.cu", "update.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-shared",
@@ -129,7 +129,7 @@ _lib = None
 # stream the call was given (bench.py's per-kernel roofline pass).
 CALLS = {}
 PROFILER = None
-_COMPUTE = ("b200dp_augment_u8_bf16", "b200dp_resized_crop_u8_bf16", "b200dp_bn_fwd_stats", "b200dp_bn_fwd_stats_noalloc", "b200dp_bn_fwd_apply", "b200dp_bn_inference",
+_COMPUTE = ("b200dp_augment_u8_bf16", "b200dp_resized_crop_u8_bf16", "b200dp_maxpool_fwd", "b200dp_maxpool_bwd", "b200dp_bn_fwd_stats", "b200dp_bn_fwd_stats_noalloc", "b200dp_bn_fwd_apply", "b200dp_bn_inference",
             "b200dp_bn_bwd_reduce", "b200dp_bn_bwd_apply", "b200dp_bucket_pack", "b200dp_allreduce_update",
             "b200dp_comm_barrier", "b200dp_bn_forward", "b200dp_bn_backward")
 
@@ -165,6 +165,8 @@ _SIGNATURES = {
                                        POINTER(c_float), POINTER(c_float), _VP, _VP]),
     "b200dp_resized_crop_u8_bf16": (c_int, [_VP, c_int, c_int, c_int, _VP, c_int, c_int,
                                             POINTER(c_float), POINTER(c_float), _VP, _VP]),
+    "b200dp_maxpool_fwd": (c_int, [_VP, _VP, _VP, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, _VP]),
+    "b200dp_maxpool_bwd": (c_int, [_VP, _VP, _VP, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, _VP]),
     "b200dp_bn_scratch_bytes": (c_size_t, [c_int]),
     "b200dp_bn_fwd_stats": (c_int, [_VP, c_int, c_int64, c_int, _VP, _VP, _VP, c_uint32, _VP]),
     "b200dp_bn_fwd_stats_noalloc": (c_int, [_VP, c_int, c_int64, c_int, _VP, _VP]),

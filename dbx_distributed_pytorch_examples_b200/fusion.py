@@ -18,6 +18,7 @@ import types
 
 import torch.nn as nn
 
+from . import pool
 from .syncbn import B200SyncBatchNorm
 
 
@@ -89,4 +90,7 @@ def fuse_bn_relu(model: nn.Module) -> nn.Module:
             # the stem's ReLU module is used nowhere else in these models
             m.bn1.fuse_relu = True
             m.relu = nn.Identity()
+            # the pooling layer after it (setup/resnet18.py:37,58): same arithmetic, one kernel each way
+            if pool.supported(m.maxpool):
+                m.maxpool = pool.B200MaxPool2d.from_module(m.maxpool)
     return model

@@ -111,6 +111,28 @@ int b200dp_resized_crop_u8_bf16(const uint8_t* src, int B, int Hs, int Ws,
                                 b200dp_stream_t stream);
 
 /* ------------------------------------------------------------------------
+ * (2b) NHWC max pooling, the layer that follows the stem's BN + ReLU.
+ *
+ * Replaces nn.MaxPool2d(kernel_size=3, stride=2, padding=1) as the reference model applies
+ * it to relu(bn1(conv1(x))) (setup/resnet18.py:37,58) and as torchvision's resnet18/50 do
+ * (01_torch_distributor/02_cifar_torch_distributor_resnet.py:146,
+ * 03_tiny_imagenet_torch_distributor_resnet.py:130).  Arithmetic is torch's max_pool2d
+ * (ATen max_pool2d_with_indices: the window is scanned rows then columns and a value is
+ * taken when `val > max || isnan(val)`, so the first maximum wins a tie); the backward
+ * routes each output gradient to that one input position and sums in fp32.
+ *
+ *  x / dx   [N, H, W, C] (channels_last), float32 or bfloat16, 16-byte aligned
+ *  y / dy   [N, Ho, Wo, C], Ho = (H + 2*pad - k) / stride + 1 (floor), same for Wo
+ *  idx      uint8 [N, Ho, Wo, C]: which tap of the k*k window won (row * k + column,
+ *           relative to the unclipped window), written by fwd, read by bwd; 8-byte aligned
+ *  k <= 3, pad <= k/2, C a multiple of 8 (bf16) / 4 (fp32); dilation 1, ceil_mode off.
+ * ---------------------------------------------------------------------- */
+int b200dp_maxpool_fwd(const void* x, void* y, uint8_t* idx, int dtype, int N, int H, int W, int C,
+                       int k, int stride, int pad, b200dp_stream_t stream);
+int b200dp_maxpool_bwd(const void* dy, const uint8_t* idx, void* dx, int dtype, int N, int H, int W,
+                       int C, int k, int stride, int pad, b200dp_stream_t stream);
+
+/* ------------------------------------------------------------------------
  * (2) SyncBatchNorm, NHWC ([M, C] row-major, M = N*H*W), training mode.
  *
  * Together these four take over TORCH/nn/modules/_functions.py:7-209

@@ -91,6 +91,26 @@ def gen_resample(name, B, src_hw, out, random_resized_crop, mean, std, seed):
                         random_resized_crop=int(random_resized_crop))
 
 
+def gen_maxpool():
+    """F.max_pool2d + autograd on inputs full of ties (ReLU output, coarse values): nn.MaxPool2d(3, 2, 1) as in
+    setup/resnet18.py:37,58 plus a 2x2/2 and a 3x3/1 window on odd sizes."""
+    g = torch.Generator().manual_seed(77)
+    out = {}
+    for tag, (N, C, H, W, k, s, p) in {"stem": (3, 16, 14, 14, 3, 2, 1), "odd": (2, 8, 9, 11, 3, 1, 1),
+                                        "k2": (2, 8, 7, 10, 2, 2, 0), "k3p0": (2, 8, 8, 8, 3, 2, 0)}.items():
+        x = torch.relu(torch.randn(N, C, H, W, generator=g)).mul(4).round().div(4)  # many exact ties, many zeros
+        x = x.contiguous(memory_format=torch.channels_last).requires_grad_(True)
+        y = F.max_pool2d(x, k, s, p)
+        dy = torch.randn(y.shape, generator=g)
+        y.backward(dy)
+        out[f"{tag}_geom"] = np.array([k, s, p])
+        out[f"{tag}_x"] = x.detach().permute(0, 2, 3, 1).contiguous().numpy()
+        out[f"{tag}_y"] = y.detach().permute(0, 2, 3, 1).contiguous().numpy()
+        out[f"{tag}_dy"] = dy.permute(0, 2, 3, 1).contiguous().numpy()
+        out[f"{tag}_dx"] = x.grad.permute(0, 2, 3, 1).contiguous().numpy()
+    np.savez_compressed(os.path.join(GOLD, "maxpool.npz"), **out)
+
+
 def gen_syncbn():
     torch.manual_seed(7)
     C, eps, mom = 16, 1e-5, 0.1
@@ -264,6 +284,7 @@ if __name__ == "__main__":
         gen_resample("resample_rrc224.npz", 2, (256, 256), 224, True, *imagenet, 7)
         gen_resample("resample_resize64.npz", 6, (32, 32), 64, False, *imagenet, 99)
         gen_resample("resample_down24.npz", 4, (75, 100), 24, False, *imagenet, 5)
+        gen_maxpool()
     if a.only_resample:
         sys.exit(0)
     if not a.only_ddp:

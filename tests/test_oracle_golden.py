@@ -97,3 +97,16 @@ def test_sampler_and_bucket_assignment(golden):
     for b, members in enumerate(buckets):
         bucket_of[members] = b
     assert np.array_equal(bucket_of, g["resnet18_bucket_of_param"])
+
+
+def test_maxpool_forward_backward(golden):
+    """oracle/pool_ref.py against torch's own max_pool2d + autograd on tie-heavy inputs."""
+    from oracle import pool_ref
+    g = golden("maxpool.npz")
+    for tag in ("stem", "odd", "k2", "k3p0"):
+        k, s, p = (int(v) for v in g[f"{tag}_geom"])
+        x = g[f"{tag}_x"]
+        y, tap = pool_ref.maxpool_forward(x, k, s, p)
+        assert np.array_equal(y, g[f"{tag}_y"])
+        dx = pool_ref.maxpool_backward(g[f"{tag}_dy"], tap, x.shape[1:3], k, s, p)
+        np.testing.assert_allclose(dx, g[f"{tag}_dx"], rtol=1e-6, atol=1e-6)
