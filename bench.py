@@ -177,6 +177,10 @@ def algorithmic_bytes(name, a):
         return a[6] * a[7] * es(a[5]) * (3 + {2: 1, 3: 0.25}.get(a[14], 0) + (1 if a[4] else 0))
     if name == "b200dp_augment_u8_bf16":
         return a[1] * a[6] * a[7] * 3 * 3
+    if name in ("b200dp_maxpool_fwd", "b200dp_maxpool_bwd"):  # x (or dx) once, y (or dy) + one tap byte per element
+        N, H, W, C, k, st, pad = a[4], a[5], a[6], a[7], a[8], a[9], a[10]
+        ho, wo = (H + 2 * pad - k) // st + 1, (W + 2 * pad - k) // st + 1
+        return N * C * (H * W * es(a[3]) + ho * wo * (es(a[3]) + 1))
     if name == "b200dp_allreduce_update":  # world 1: g + master r/w + momentum r/w + param copy
         e = es(a[2])
         return a[6] * (e + 8 + 8 + (e if a[7] else 0))
