@@ -501,6 +501,7 @@ bn_stats_kernel(const T* __restrict__ x, int64_t M, int C, void* scratch, float*
 #pragma unroll
   for (int k = 0; k < N; ++k) mean[k] = m2[k] = 0.f;
 
+  pdl_wait();  // no-op unless launched as a programmatic dependent of the kernel that writes x
   if (chan_ok) {
     const RowRange rr = my_rows(M, r);
     // rev: walk this thread's rows from the last to the first (see bn_order())
@@ -753,6 +754,7 @@ bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T*
   float s1[N], s2[N];
 #pragma unroll
   for (int k = 0; k < N; ++k) s1[k] = s2[k] = 0.f;
+  pdl_wait();  // no-op unless launched as a programmatic dependent of the kernel that writes dy
   if (chan_ok) {
     const RowRange rr = my_rows(M, r);
     const int64_t step = rev ? -rr.step * C : rr.step * C;
@@ -1008,6 +1010,15 @@ int bn_order() {
   return order;
 }
 
+// The reduction kernels are launched as programmatic dependents of whatever precedes them in the
+// stream (a convolution, usually): when that kernel signals early, their launch latency and set-up
+// overlap its tail; they block in griddepcontrol.wait before the first load.  B200DP_BN_PDL_FIRST=0
+// turns it off.
+bool pdl_first() {
+  static const bool on = [] { const char* e = getenv("B200DP_BN_PDL_FIRST"); return !(e && e[0] == '0'); }();
+  return on;
+}
+
 // Launch with (or without) the programmatic-stream-serialization attribute.
 thread_local bool t_pdl_next = false;  // set by b200dp_bn_forward / _backward around their second launch
 
@@ -1063,12 +1074,12 @@ extern "C" int b200dp_bn_fwd_stats(const void* x, int dtype, int64_t M, int C, v
   cudaStream_t s = (cudaStream_t)stream;
   if (dtype == B200DP_BF16) {
     const Grid2 g = plan_grid_clustered<__nv_bfloat16>(M, C, max_active_clusters(bn_stats_kernel<__nv_bfloat16>));
-    bn_stats_kernel<__nv_bfloat16><<<dim3(g.gx, g.gy), kT, 0, s>>>(
-        static_cast<const __nv_bfloat16*>(x), M, C, scratch, stats_local, P, seq, bn_order() & 1);
+    B200DP_CUDA_TRY(launch_ex(bn_stats_kernel<__nv_bfloat16>, dim3(g.gx, g.gy), s, pdl_first(),
+                              static_cast<const __nv_bfloat16*>(x), M, C, scratch, stats_local, P, seq, bn_order() & 1));
   } else {
     const Grid2 g = plan_grid_clustered<float>(M, C, max_active_clusters(bn_stats_kernel<float>));
-    bn_stats_kernel<float><<<dim3(g.gx, g.gy), kT, 0, s>>>(static_cast<const float*>(x), M, C,
-                                                           scratch, stats_local, P, seq, bn_order() & 1);
+    B200DP_CUDA_TRY(launch_ex(bn_stats_kernel<float>, dim3(g.gx, g.gy), s, pdl_first(), static_cast<const float*>(x), M, C,
+                              scratch, stats_local, P, seq, bn_order() & 1));
   }
   B200DP_LAUNCH_CHECK();
   return B200DP_OK;
@@ -1214,9 +1225,9 @@ int launch_bwd_reduce(const void* dy, const void* x, const void* yo, int64_t M, 
   const T* px = static_cast<const T*>(x);
   const T* py = static_cast<const T*>(yo);
 #define B200DP_BWD_REDUCE(R)                                                                   \
-  bn_bwd_reduce_kernel<T, R><<<grid, kT, 0, s>>>(pdy, px, py, M, C, save_mean, save_invstd,    \
-                                                 weight, bias, scratch, sums_local,            \
-                                                 grad_weight, grad_bias, P, seq, (bn_order() >> 2) & 1)
+  B200DP_CUDA_TRY(launch_ex(bn_bwd_reduce_kernel<T, R>, grid, s, pdl_first(), pdy, px, py, M, C, save_mean,   \
+                            save_invstd, weight, bias, scratch, sums_local, grad_weight, grad_bias, P, seq,  \
+                            (bn_order() >> 2) & 1))
   if (relu == 0) B200DP_BWD_REDUCE(0);
   else if (relu == 1) B200DP_BWD_REDUCE(1);
   else if (relu == 2) B200DP_BWD_REDUCE(2);
