@@ -179,7 +179,7 @@ _SIGNATURES = {
     "b200dp_bn_bwd_apply": (c_int, [_VP, _VP, _VP, _VP, _VP, c_int, c_int64, c_int, _VP, _VP, _VP,
                                     _VP, _VP, _VP, c_int, _VP, c_uint32, _VP]),
     "b200dp_bn_forward": (c_int, [_VP, _VP, _VP, c_int, c_int64, c_int, _VP, _VP, _VP, _VP, c_float, c_float,
-                                  _VP, _VP, _VP, c_int, _VP, c_uint32, _VP, _VP]),
+                                  _VP, _VP, _VP, c_int, _VP, c_uint32, _VP, _VP, _VP]),
     "b200dp_bn_backward": (c_int, [_VP, _VP, _VP, _VP, _VP, c_int, c_int64, c_int, _VP, _VP, _VP, c_int, _VP, _VP,
                                    _VP, _VP, _VP, c_uint32, _VP]),
     "b200dp_comm_create": (c_int, [c_int, c_int, c_size_t, POINTER(_VP)]),

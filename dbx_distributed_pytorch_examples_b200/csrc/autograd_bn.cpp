@@ -27,7 +27,7 @@ using torch::autograd::variable_list;
 
 typedef int (*fwd_fn)(const void*, const void*, void*, int, int64_t, int, void*, float*, const float*,
                       const float*, float, float, float*, float*, float*, int, void*, uint32_t, void*,
-                      uint32_t*);
+                      uint32_t*, int64_t*);
 typedef int (*bwd_fn)(const void*, const void*, const void*, void*, void*, int, int64_t, int, const float*,
                       const float*, const float*, int, void*, float*, float*, float*, void*, uint32_t,
                       void*);
@@ -94,7 +94,7 @@ class FusedSyncBN : public torch::autograd::Function<FusedSyncBN> {
   static Tensor forward(AutogradContext* ctx, const Tensor& x_in, const c10::optional<Tensor>& residual_in,
                         const c10::optional<Tensor>& weight, const c10::optional<Tensor>& bias,
                         int64_t running_mean, int64_t running_var, double eps, double momentum, bool relu,
-                        int64_t comm, int64_t world, bool mask_words) {
+                        int64_t comm, int64_t world, bool mask_words, int64_t batches_tracked) {
     TORCH_CHECK(g_fwd != nullptr, "_b200dp_autograd.bind() has not been called");
     Tensor x = as_rows(x_in);
     const int64_t C = x.size(1);
@@ -125,7 +125,8 @@ class FusedSyncBN : public torch::autograd::Function<FusedSyncBN> {
     g_fwd_calls.fetch_add(1, std::memory_order_relaxed);
     check(g_fwd(x.data_ptr(), ptr(residual), y.data_ptr(), dt, M, (int)C, bn_scratch(x.device(), stream), aux_p,
                 (const float*)ptr(w32), (const float*)ptr(b32), (float)eps, (float)momentum, (float*)running_mean,
-                (float*)running_var, sv, relu ? 1 : 0, h, seq, stream, (uint32_t*)ptr(maskw)),
+                (float*)running_var, sv, relu ? 1 : 0, h, seq, stream, (uint32_t*)ptr(maskw),
+                (int64_t*)batches_tracked),
           "b200dp_bn_forward");
     // ReLU mask in the backward: recomputed from x when nothing was added, else from y (or the mask words)
     const int relu_mode = !relu ? 0 : (!has_res ? 1 : (maskw.defined() ? 3 : 2));
@@ -189,15 +190,17 @@ class FusedSyncBN : public torch::autograd::Function<FusedSyncBN> {
       const auto bt = (at::ScalarType)ctx->saved_data["b_dtype"].toInt();
       if (bt != at::kFloat) gb = gb.to(bt);
     }
-    return {dx, dres, gw, gb, Tensor(), Tensor(), Tensor(), Tensor(), Tensor(), Tensor(), Tensor(), Tensor()};
+    return {dx, dres, gw, gb, Tensor(), Tensor(), Tensor(), Tensor(), Tensor(), Tensor(), Tensor(), Tensor(), Tensor()};
   }
 };
 
 Tensor fused_syncbn(const Tensor& x, const c10::optional<Tensor>& residual, const c10::optional<Tensor>& weight,
                     const c10::optional<Tensor>& bias, int64_t running_mean, int64_t running_var, double eps,
-                    double momentum, bool relu, int64_t comm, int64_t world, bool mask_words) {
+                    double momentum, bool relu, int64_t comm, int64_t world, bool mask_words,
+                    int64_t batches_tracked) {
+  // batches_tracked: address of the layer's int64 num_batches_tracked on the device (0: the caller counts)
   return FusedSyncBN::apply(x, residual, weight, bias, running_mean, running_var, eps, momentum, relu, comm, world,
-                            mask_words);
+                            mask_words, batches_tracked);
 }
 
 void bind(const std::string& lib_path) {

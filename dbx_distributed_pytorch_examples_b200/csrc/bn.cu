@@ -591,6 +591,7 @@ struct FwdArgs {
   // optional output: one 32-bit word per 16-byte vector of y, bit j = (y[j] > 0)
   uint32_t* maskw;
   int rev;  // walk the rows from the last to the first
+  long long* batches_tracked;  // optional: the layer's num_batches_tracked counter, incremented once
 };
 
 // Per-channel coefficients of one chunk are worked out once per CTA, by its first kCV
@@ -627,6 +628,7 @@ __global__ void __launch_bounds__(kT, kOccFwd) bn_fwd_apply_kernel(FwdArgs A, b2
   ring.init(smem);
   const int nrows = chan_ok ? rr.count : 0;
   ring.prime(nrows, ptrs);
+  if (A.batches_tracked && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) *A.batches_tracked += 1;
   pdl_wait();  // statistics of the producer kernel are complete and visible from here on
 
   __shared__ __align__(16) float xr[B200DP_MAX_WORLD * kCV * kXrStride];
@@ -1169,13 +1171,13 @@ int launch_fwd_apply(const FwdArgs& A, bool relu, const b200dp_peers& P, uint32_
 }
 }  // namespace
 
-extern "C" int b200dp_bn_fwd_apply(const void* x, const void* residual, void* y, int dtype,
-                                   int64_t M, int C, const float* stats_local,
-                                   const float* weight, const float* bias, float eps,
-                                   float momentum, float* running_mean, float* running_var,
-                                   float* save_mean, float* save_invstd, float* save_count,
-                                   int relu, b200dp_comm* comm, uint32_t seq,
-                                   b200dp_stream_t stream, uint32_t* relu_mask) {
+static int fwd_apply_impl(const void* x, const void* residual, void* y, int dtype,
+                          int64_t M, int C, const float* stats_local,
+                          const float* weight, const float* bias, float eps,
+                          float momentum, float* running_mean, float* running_var,
+                          float* save_mean, float* save_invstd, float* save_count,
+                          int relu, b200dp_comm* comm, uint32_t seq,
+                          b200dp_stream_t stream, uint32_t* relu_mask, int64_t* batches_tracked) {
   int rc = check_common(x, residual, y, dtype, M, C);
   if (rc) return rc;
   if (relu_mask && (dtype != B200DP_BF16 || !relu)) return B200DP_EUNSUPPORTED;
@@ -1183,11 +1185,24 @@ extern "C" int b200dp_bn_fwd_apply(const void* x, const void* residual, void* y,
   if (M > 0 && !y) return B200DP_EINVAL;
   if ((rc = check_comm(comm, seq))) return rc;
   FwdArgs A{x, residual, y, M, C, stats_local, weight, bias, eps, momentum, running_mean,
-            running_var, save_mean, save_invstd, save_count, nullptr, nullptr, relu_mask, (bn_order() >> 1) & 1};
+            running_var, save_mean, save_invstd, save_count, nullptr, nullptr, relu_mask, (bn_order() >> 1) & 1,
+            reinterpret_cast<long long*>(batches_tracked)};
   const b200dp_peers P = b200dp_make_peers(comm);
   cudaStream_t s = (cudaStream_t)stream;
   return dtype == B200DP_BF16 ? launch_fwd_apply<__nv_bfloat16>(A, relu != 0, P, seq, s)
                               : launch_fwd_apply<float>(A, relu != 0, P, seq, s);
+}
+
+extern "C" int b200dp_bn_fwd_apply(const void* x, const void* residual, void* y, int dtype,
+                                   int64_t M, int C, const float* stats_local,
+                                   const float* weight, const float* bias, float eps,
+                                   float momentum, float* running_mean, float* running_var,
+                                   float* save_mean, float* save_invstd, float* save_count,
+                                   int relu, b200dp_comm* comm, uint32_t seq,
+                                   b200dp_stream_t stream, uint32_t* relu_mask) {
+  return fwd_apply_impl(x, residual, y, dtype, M, C, stats_local, weight, bias, eps, momentum, running_mean,
+                        running_var, save_mean, save_invstd, save_count, relu, comm, seq, stream, relu_mask,
+                        nullptr);
 }
 
 extern "C" int b200dp_bn_inference(const void* x, const void* residual, void* y, int dtype,
@@ -1201,7 +1216,7 @@ extern "C" int b200dp_bn_inference(const void* x, const void* residual, void* y,
   if (M == 0) return B200DP_OK;
   if (!y) return B200DP_EINVAL;
   FwdArgs A{x, residual, y, M, C, nullptr, weight, bias, eps, 0.f, nullptr, nullptr, nullptr,
-            nullptr, nullptr, running_mean, running_var, nullptr, 0};
+            nullptr, nullptr, running_mean, running_var, nullptr, 0, nullptr};
   const b200dp_peers P = b200dp_make_peers(nullptr);
   cudaStream_t s = (cudaStream_t)stream;
   return dtype == B200DP_BF16 ? launch_fwd_apply<__nv_bfloat16>(A, relu != 0, P, 0, s)
@@ -1315,14 +1330,16 @@ extern "C" int b200dp_bn_forward(const void* x, const void* residual, void* y, i
                                  int C, void* scratch, float* stats_local, const float* weight,
                                  const float* bias, float eps, float momentum, float* running_mean,
                                  float* running_var, float* save, int relu, b200dp_comm* comm,
-                                 uint32_t seq, b200dp_stream_t stream, uint32_t* relu_mask) {
+                                 uint32_t seq, b200dp_stream_t stream, uint32_t* relu_mask,
+                                 int64_t* num_batches_tracked) {
   if (!save) return B200DP_EINVAL;
+  if ((uintptr_t)num_batches_tracked & 7) return B200DP_EALIGN;
   int rc = b200dp_bn_fwd_stats(x, dtype, M, C, scratch, stats_local, comm, seq, stream);
   if (rc) return rc;
   t_pdl_next = true;  // the normalise kernel may start while the statistics kernel finishes its tail
-  rc = b200dp_bn_fwd_apply(x, residual, y, dtype, M, C, stats_local, weight, bias, eps, momentum,
-                           running_mean, running_var, save, save + C, save + 2 * C, relu, comm, seq,
-                           stream, relu_mask);
+  rc = fwd_apply_impl(x, residual, y, dtype, M, C, stats_local, weight, bias, eps, momentum,
+                      running_mean, running_var, save, save + C, save + 2 * C, relu, comm, seq,
+                      stream, relu_mask, num_batches_tracked);
   t_pdl_next = false;
   return rc;
 }

@@ -92,7 +92,7 @@ class _FusedSyncBN(torch.autograd.Function):
     """y = act(bn(x) [+ residual]) with batch statistics shared across ranks."""
 
     @staticmethod
-    def forward(ctx, x, residual, weight, bias, running_mean, running_var, eps, momentum, relu, comm):
+    def forward(ctx, x, residual, weight, bias, running_mean, running_var, eps, momentum, relu, comm, count_ptr=0):
         lib = _lib.lib()
         x = _as_rows(x)
         C = x.shape[1]
@@ -133,12 +133,13 @@ class _FusedSyncBN(torch.autograd.Function):
             if _lib.PROFILER is None and fast is not None:
                 _lib.CALLS["b200dp_bn_forward"] = _lib.CALLS.get("b200dp_bn_forward", 0) + 1
                 rc = fast.bn_forward(xp, rp, yp, dt, M, C, scr, aux_p, wp, bp, float(eps), float(momentum), rmp, rvp, sv,
-                                     int(bool(relu)), h.value if h else 0, seq, stream, mp)
+                                     int(bool(relu)), h.value if h else 0, seq, stream, mp, count_ptr)
                 if rc:
                     _lib.check(rc, "b200dp_bn_forward")
             elif _lib.PROFILER is None:
                 _lib.check(lib.b200dp_bn_forward(xp, rp, yp, dt, M, C, scr, aux_p, wp, bp, float(eps), float(momentum),
-                                                 rmp, rvp, sv, int(bool(relu)), h, seq, stream, mp), "b200dp_bn_forward")
+                                                 rmp, rvp, sv, int(bool(relu)), h, seq, stream, mp, count_ptr or None),
+                           "b200dp_bn_forward")
             else:  # per-kernel timing pass: the same two launches through their own entry points
                 _lib.check(lib.b200dp_bn_fwd_stats(xp, dt, M, C, scr, aux_p, h, seq, stream), "b200dp_bn_fwd_stats")
                 _lib.check(lib.b200dp_bn_fwd_apply(xp, rp, yp, dt, M, C, aux_p, wp, bp, float(eps), float(momentum),
@@ -202,7 +203,7 @@ class _FusedSyncBN(torch.autograd.Function):
             gw = gw.to(weight.dtype)
         if gb is not None and bias.dtype != torch.float32:
             gb = gb.to(bias.dtype)
-        return dx, dres, gw, gb, None, None, None, None, None, None
+        return dx, dres, gw, gb, None, None, None, None, None, None, None
 
 
 class _FusedBNInference(torch.autograd.Function):
@@ -302,8 +303,14 @@ class B200SyncBatchNorm(_BatchNorm):
             factor = 0.0
         else:
             factor = self.momentum
+        count_ptr = 0
         if self.training and self.track_running_stats:
-            self.num_batches_tracked.add_(1)
+            if self.momentum is None or _lib.PROFILER is not None or not self.num_batches_tracked.is_cuda:
+                self.num_batches_tracked.add_(1)
+            else:
+                # the forward kernel adds the 1 (b200dp_bn_forward's last argument): one tiny torch kernel
+                # less per layer and step, and the statistics kernel stays directly behind the convolution
+                count_ptr = self.num_batches_tracked.data_ptr()
             if self.momentum is None:
                 factor = 1.0 / self.num_batches_tracked.item()
             else:
@@ -330,9 +337,9 @@ class B200SyncBatchNorm(_BatchNorm):
                                     0 if running_var is None else running_var.data_ptr(),
                                     self.eps, factor, self.fuse_relu,
                                     comm.handle.value if comm is not None else 0,
-                                    comm.world if comm is not None else 1, _USE_MASK_WORDS)
+                                    comm.world if comm is not None else 1, _USE_MASK_WORDS, count_ptr)
         return _FusedSyncBN.apply(input, residual, self.weight, self.bias, running_mean, running_var,
-                                  self.eps, factor, self.fuse_relu, comm)
+                                  self.eps, factor, self.fuse_relu, comm, count_ptr)
 
     @classmethod
     def convert_sync_batchnorm(cls, module, process_group=None):

@@ -254,7 +254,10 @@ int b200dp_bn_forward(const void* x, const void* residual, void* y, int dtype,
                       const float* weight, const float* bias, float eps,
                       float momentum, float* running_mean, float* running_var,
                       float* save, int relu, b200dp_comm* comm, uint32_t seq,
-                      b200dp_stream_t stream, uint32_t* relu_mask);
+                      b200dp_stream_t stream, uint32_t* relu_mask,
+                      int64_t* num_batches_tracked /* optional: the layer's int64 counter on the device,
+                         incremented by one (TORCH/nn/modules/batchnorm.py:760-763 does it with a kernel
+                         of its own per layer and step); NULL to leave it to the caller */);
 int b200dp_bn_backward(const void* dy, const void* x, const void* y_out, void* dx,
                        void* d_residual, int dtype, int64_t M, int C,
                        const float* save, const float* weight, const float* bias,

@@ -198,3 +198,27 @@ def test_cpp_autograd_node_errors_and_frozen_inputs():
     y = bn(torch.randn(2, 4, 3, 3, device="cuda").contiguous())
     assert y.shape == (2, 4, 3, 3)
     assert b200.B200SyncBatchNorm(4).cuda()(torch.randn(6, 4, device="cuda")).shape == (6, 4)
+
+
+def test_num_batches_tracked_is_counted_by_the_kernel(monkeypatch):
+    """The forward kernel increments the layer's counter (no separate torch kernel); momentum=None,
+    eval mode and the python node count like nn.BatchNorm2d does."""
+    from dbx_distributed_pytorch_examples_b200 import _lib
+    x = torch.randn(4, 16, 5, 5, device="cuda")
+    bn = b200.B200SyncBatchNorm(16).cuda()
+    ref = torch.nn.BatchNorm2d(16).cuda()
+    for _ in range(3):
+        bn(x); ref(x)
+    assert int(bn.num_batches_tracked) == int(ref.num_batches_tracked) == 3
+    bn.eval(); bn(x)
+    assert int(bn.num_batches_tracked) == 3
+    bn.train()
+    with torch.no_grad():
+        bn(x)
+    assert int(bn.num_batches_tracked) == 4
+    monkeypatch.setattr(_lib, "_native", False)   # the python autograd node passes the same pointer
+    bn(x)
+    assert int(bn.num_batches_tracked) == 5
+    cum = b200.B200SyncBatchNorm(16, momentum=None).cuda()
+    cum(x); cum(x)
+    assert int(cum.num_batches_tracked) == 2

@@ -202,8 +202,8 @@ def test_autograd_extension_loads_and_binds():
     # argument checks happen before any CUDA call, so they can be exercised here; they must come out as
     # python exceptions (an extension built with a compiler that brings its own libstdc++ crashed instead)
     with pytest.raises(ValueError, match="more than 1 value per channel"):
-        nat.fused_syncbn(torch.randn(1, 32), None, None, None, 0, 0, 1e-5, 0.1, False, 0, 1, False)
+        nat.fused_syncbn(torch.randn(1, 32), None, None, None, 0, 0, 1e-5, 0.1, False, 0, 1, False, 0)
     with pytest.raises(ValueError, match="residual must have the shape"):
-        nat.fused_syncbn(torch.randn(4, 8, 3, 3), torch.randn(4, 8, 3, 2), None, None, 0, 0, 1e-5, 0.1, False, 0, 1, False)
+        nat.fused_syncbn(torch.randn(4, 8, 3, 3), torch.randn(4, 8, 3, 2), None, None, 0, 0, 1e-5, 0.1, False, 0, 1, False, 0)
     with pytest.raises(RuntimeError, match="float32 and bfloat16"):
-        nat.fused_syncbn(torch.randn(4, 8).double(), None, None, None, 0, 0, 1e-5, 0.1, False, 0, 1, False)
+        nat.fused_syncbn(torch.randn(4, 8).double(), None, None, None, 0, 0, 1e-5, 0.1, False, 0, 1, False, 0)

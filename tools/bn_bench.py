@@ -72,7 +72,7 @@ def main():
         }
         nb = lambda k: calls[k][1]  # noqa: E731
         calls["fwd(1 call)"] = (lambda: lib.b200dp_bn_forward(P(x), P(r), P(y), code, M, C, P(scratch), P(stats), P(w), P(b),
-                                                             1e-5, 0.1, None, None, P(save), 1, None, 0, s, P(mk)),
+                                                             1e-5, 0.1, None, None, P(save), 1, None, 0, s, P(mk), None),
                                 nb("stats") + nb("fwd_apply"))
         calls["bwd(1 call)"] = (lambda: lib.b200dp_bn_backward(P(dy), P(x), P(mk if res else y), P(dx), P(dr), code, M, C, P(save), P(w), P(b),
                                                               mode, P(scratch), P(sums), P(gw), P(gb), None, 0, s),
