@@ -43,15 +43,17 @@ errstr_fn g_errstr = nullptr;
 std::atomic<long long> g_fwd_calls{0}, g_bwd_calls{0};
 
 std::mutex g_scratch_mu;
-std::map<std::pair<int, void*>, Tensor> g_scratch;  // zero-filled reduction scratch per (device, stream)
+// zero-filled reduction scratch per (device, stream); never destroyed: a static destructor would hand
+// CUDA memory back after torch's allocator has gone at interpreter exit
+auto* g_scratch = new std::map<std::pair<int, void*>, Tensor>();
 
 void* bn_scratch(const at::Device& dev, void* stream) {
   std::lock_guard<std::mutex> lk(g_scratch_mu);
   auto key = std::make_pair((int)dev.index(), stream);
-  auto it = g_scratch.find(key);
-  if (it == g_scratch.end()) {
+  auto it = g_scratch->find(key);
+  if (it == g_scratch->end()) {
     const int64_t n = (int64_t)g_scratch_bytes(0);
-    it = g_scratch.emplace(key, at::zeros({n}, at::TensorOptions().dtype(at::kByte).device(dev))).first;
+    it = g_scratch->emplace(key, at::zeros({n}, at::TensorOptions().dtype(at::kByte).device(dev))).first;
   }
   return it->second.data_ptr();
 }
