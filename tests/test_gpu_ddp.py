@@ -209,3 +209,27 @@ def test_feed_and_loss_reader():
         seen.extend(lab.cpu().tolist())
     assert sorted(seen) == list(range(n))
     assert reader.flush() == pytest.approx(fed)
+
+
+def test_200_step_loss_curve_full_stack_fp32():
+    """north_star's training criterion on one GPU: 200 steps of the reference ResNet-18 recipe
+    (SGD 1e-3, momentum 0.5, batch 128: 01_basic_torch_distributor.py:294, BASELINE config 1 sizes) with the
+    whole fused stack — SyncBN+ReLU(+add), stem pooling, bucket kernel with the fused SGD — against stock
+    torch in fp32 on the same data: every loss within 1 %."""
+    ref, m = make_pair()
+    m = b200.fuse_bn_relu(b200.convert_sync_batchnorm(m)).to(memory_format=torch.channels_last)
+    assert isinstance(m.maxpool, b200.B200MaxPool2d)
+    ddp = b200.B200DDP(m, device_ids=[0])
+    o_ref = torch.optim.SGD(ref.parameters(), lr=1e-3, momentum=0.5)
+    o_our = ddp.fuse_optimizer(torch.optim.SGD(ddp.parameters(), lr=1e-3, momentum=0.5))
+    worst = 0.0
+    for step in range(200):
+        x, y = batch(step, 128)
+        o_ref.zero_grad(); o_our.zero_grad()
+        l_ref = F.cross_entropy(ref(x), y); l_ref.backward(); o_ref.step()
+        l_our = F.cross_entropy(ddp(x.contiguous(memory_format=torch.channels_last)), y); l_our.backward(); o_our.step()
+        if step % 10 == 9 or step < 3:
+            worst = max(worst, abs(float(l_our) - float(l_ref)) / float(l_ref))
+    assert worst < 0.01, worst
+    assert int(m.bn1.num_batches_tracked) == int(ref.bn1.num_batches_tracked) == 200
+    torch.testing.assert_close(m.bn1.running_var, ref.bn1.running_var, rtol=1e-3, atol=1e-5)
