@@ -16,7 +16,7 @@ of include/b200dp.h).  There is no CPU or eager fallback: without the built
 library or without a GPU the entry points raise.
 """
 from ._lib import B200DPError, build  # noqa: F401
-from .comm import Communicator  # noqa: F401
+from .comm import Communicator, all_gather_scalars  # noqa: F401
 from .ddp import B200DDP, prepare_model  # noqa: F401
 from .distributor import DeepspeedTorchDistributor, TorchDistributor  # noqa: F401
 from .feed import DeviceFeeder, LossReader, PinnedImageDataset, ShardedBatchSampler  # noqa: F401
@@ -28,6 +28,6 @@ from .transform import (BatchTransform, ResizeBatchTransform, draw_crop_flip_par
 
 __all__ = [
     "B200DDP", "prepare_model", "B200SyncBatchNorm", "BatchTransform", "Communicator", "TorchDistributor",
-    "DeepspeedTorchDistributor", "convert_sync_batchnorm", "fuse_bn_relu", "draw_crop_flip_params", "B200MaxPool2d", "ResizeBatchTransform", "draw_resized_crop_flip_params",
+    "DeepspeedTorchDistributor", "convert_sync_batchnorm", "fuse_bn_relu", "draw_crop_flip_params", "all_gather_scalars", "B200MaxPool2d", "ResizeBatchTransform", "draw_resized_crop_flip_params",
     "B200DPError", "build", "DeviceFeeder", "LossReader", "PinnedImageDataset", "ShardedBatchSampler",
 ]

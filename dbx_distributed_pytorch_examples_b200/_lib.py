@@ -131,7 +131,7 @@ CALLS = {}
 PROFILER = None
 _COMPUTE = ("b200dp_augment_u8_bf16", "b200dp_resized_crop_u8_bf16", "b200dp_maxpool_fwd", "b200dp_maxpool_bwd", "b200dp_bn_fwd_stats", "b200dp_bn_fwd_stats_noalloc", "b200dp_bn_fwd_apply", "b200dp_bn_inference",
             "b200dp_bn_bwd_reduce", "b200dp_bn_bwd_apply", "b200dp_bucket_pack", "b200dp_allreduce_update",
-            "b200dp_comm_barrier", "b200dp_bn_forward", "b200dp_bn_backward")
+            "b200dp_comm_barrier", "b200dp_comm_all_gather32", "b200dp_bn_forward", "b200dp_bn_backward")
 
 
 class _Entry:
@@ -192,6 +192,7 @@ _SIGNATURES = {
     "b200dp_comm_heap_bytes": (c_size_t, [_VP]),
     "b200dp_comm_next_seq": (c_uint32, [_VP]),
     "b200dp_comm_barrier": (c_int, [_VP, _VP]),
+    "b200dp_comm_all_gather32": (c_int, [_VP, _VP, c_int, _VP, _VP]),
     "b200dp_comm_error": (c_int, [_VP]),
     "b200dp_bucket_pack": (c_int, [POINTER(_VP), POINTER(c_int64), POINTER(c_int64), c_int, _VP,
                                    c_int, c_float, _VP]),

@@ -78,6 +78,20 @@ class Communicator:
         with torch.cuda.device(self.device):
             _lib.check(_lib.lib().b200dp_comm_barrier(self.handle, _lib.current_stream()), "b200dp_comm_barrier")
 
+    def all_gather_scalars(self, values: torch.Tensor) -> torch.Tensor:
+        """``[world, k]`` tensor whose row r holds rank r's ``values`` (1-D, float32 or int32, on this
+        communicator's device).  One small kernel over peer memory; what the reference does with three
+        ``accelerator.gather(torch.tensor(x).to(device))`` calls per epoch
+        (04_accelerate/01_cifar_accelerate.ipynb:638-640).  Collective."""
+        if values.dim() != 1 or values.dtype not in (torch.float32, torch.int32) or not values.is_cuda:
+            raise ValueError("expected a 1-D float32 or int32 CUDA tensor")
+        values = values.contiguous()
+        out = torch.empty((self.world, values.numel()), dtype=values.dtype, device=values.device)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().b200dp_comm_all_gather32(self.handle, values.data_ptr(), values.numel(), out.data_ptr(),
+                                                           _lib.current_stream()), "b200dp_comm_all_gather32")
+        return out
+
     def check_error(self) -> None:
         """Raise if a kernel on this rank timed out waiting for a peer."""
         rc = _lib.lib().b200dp_comm_error(self.handle)
@@ -110,6 +124,17 @@ def stats_communicator(process_group=None) -> Communicator:
         comm = Communicator(process_group, heap_bytes=0)
         _stats_comms[key] = comm
     return comm
+
+
+def all_gather_scalars(values: torch.Tensor, process_group=None) -> torch.Tensor:
+    """``accelerator.gather`` for a handful of per-rank metric values: ``[world, k]`` from a 1-D float32 /
+    int32 CUDA tensor, through the process-wide communicator the SyncBatchNorm layers use.  A single
+    process (no process group, or world size 1) gets its own values back as ``[1, k]``."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(process_group) == 1:
+        if values.dim() != 1:
+            raise ValueError("expected a 1-D tensor")
+        return values.unsqueeze(0).clone()
+    return stats_communicator(process_group).all_gather_scalars(values)
 
 
 def reset_stats_communicators() -> None:

@@ -25,6 +25,25 @@ __global__ void barrier_kernel(b200dp_peers P, uint32_t seq) {
   }
 }
 
+// All-gather of k 32-bit words per rank through the SyncBN exchange slots ("LL" words: {payload, seq}
+// written with one 8-byte store into every peer's slot, polled by the reader): one kernel, one NVLink
+// traversal, no separate flag.  Thread idx handles (rank idx / k, word idx % k) in both phases.
+__global__ void gather32_kernel(b200dp_peers P, uint32_t seq, const uint32_t* __restrict__ in, int k,
+                                uint32_t* __restrict__ out) {
+  const int slot = seq % B200DP_XCHG_SLOTS;
+  const int total = k * P.world;
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+    const int peer = idx / k, j = idx - peer * k;
+    st_ll(&P.sync[peer]->bn_ll[slot][P.rank][j], __uint_as_float(in[j]), seq);
+  }
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+    const int src = idx / k, j = idx - src * k;
+    float v;
+    if (!ld_ll(&P.sync[P.rank]->bn_ll[slot][src][j], seq, &v)) atomicExch(&P.sync[P.rank]->error, 1u);
+    out[idx] = __float_as_uint(v);
+  }
+}
+
 struct ExportBlob {
   cudaIpcMemHandle_t heap;
   cudaIpcMemHandle_t sync;
@@ -143,6 +162,28 @@ extern "C" int b200dp_comm_barrier(b200dp_comm* comm, b200dp_stream_t stream) {
   if (comm->world == 1) return B200DP_OK;
   const uint32_t seq = ++comm->seq;
   barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(b200dp_make_peers(comm), seq);
+  B200DP_LAUNCH_CHECK();
+  return B200DP_OK;
+}
+
+extern "C" int b200dp_comm_all_gather32(b200dp_comm* comm, const void* in, int k, void* out,
+                                        b200dp_stream_t stream) {
+  if (!comm || k < 0) return B200DP_EINVAL;
+  if (k == 0) return B200DP_OK;
+  if (!in || !out) return B200DP_EINVAL;
+  if (((uintptr_t)in | (uintptr_t)out) & 3) return B200DP_EALIGN;
+  if (k > B200DP_XCHG_FLOATS) return B200DP_ETOOBIG;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (comm->world == 1) {
+    B200DP_CUDA_TRY(cudaMemcpyAsync(out, in, (size_t)k * 4, cudaMemcpyDeviceToDevice, s));
+    return B200DP_OK;
+  }
+  if (!comm->peers_open) return B200DP_ESTATE;
+  const uint32_t seq = ++comm->seq;
+  const int total = k * comm->world;
+  const int blocks = total <= 256 ? 1 : (total + 255) / 256 > 32 ? 32 : (total + 255) / 256;
+  gather32_kernel<<<blocks, 256, 0, s>>>(b200dp_make_peers(comm), seq, static_cast<const uint32_t*>(in), k,
+                                         static_cast<uint32_t*>(out));
   B200DP_LAUNCH_CHECK();
   return B200DP_OK;
 }

@@ -299,6 +299,13 @@ size_t b200dp_comm_heap_bytes(const b200dp_comm* comm);
 uint32_t b200dp_comm_next_seq(b200dp_comm* comm);
 /* Device-side barrier across the ranks on `stream` (a kernel that signals
  * every peer and waits for every peer); used at set-up and in tests. */
+/* All-gather of k 32-bit words (float32 or int32, bit-exact) per rank: out[r*k + j] = rank r's in[j].
+ * One small kernel over the peer-mapped exchange slots; stands for the per-epoch metric gathers of the
+ * reference (04_accelerate/01_cifar_accelerate.ipynb:638-640: three accelerator.gather calls on
+ * one-element tensors, then .sum().item()).  Collective: every rank calls it in the same order
+ * relative to its other collective calls.  k <= 2*B200DP_BN_MAX_CHANNELS + 128. */
+int b200dp_comm_all_gather32(b200dp_comm* comm, const void* in, int k, void* out,
+                             b200dp_stream_t stream);
 int b200dp_comm_barrier(b200dp_comm* comm, b200dp_stream_t stream);
 /* Synchronous read of the rank's error word: non-zero once a kernel on this
  * rank gave up waiting (about 10 s) for a peer's flag.  Takes the place of the

@@ -233,3 +233,12 @@ def test_200_step_loss_curve_full_stack_fp32():
     assert worst < 0.01, worst
     assert int(m.bn1.num_batches_tracked) == int(ref.bn1.num_batches_tracked) == 200
     torch.testing.assert_close(m.bn1.running_var, ref.bn1.running_var, rtol=1e-3, atol=1e-5)
+
+
+def test_all_gather_scalars_single_process():
+    v = torch.tensor([1.0, 2.0, 3.0], device="cuda")
+    out = b200.all_gather_scalars(v)
+    assert out.shape == (1, 3) and torch.equal(out[0], v) and out.data_ptr() != v.data_ptr()
+    c = b200.Communicator(None, heap_bytes=0)     # world 1 through the C ABI: a device copy
+    assert torch.equal(c.all_gather_scalars(v), v.view(1, 3))
+    c.destroy()

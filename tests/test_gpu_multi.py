@@ -273,6 +273,39 @@ def _w_checkpoint():
     return "ok"
 
 
+def _w_gather_scalars():
+    import torch
+    import torch.distributed as dist
+    import dbx_distributed_pytorch_examples_b200 as b200
+    rank, world = _init()
+    # the reference's per-epoch metrics: running loss (float), totals (ints) — 04_accelerate/01_cifar_accelerate.ipynb:638-640
+    for rep in range(6):   # more exchanges than there are slots
+        vals = torch.tensor([1.5 * (rank + 1) + rep, 50000.0 + rank, float("nan") if rep == 5 else 0.25], device="cuda")
+        got = b200.all_gather_scalars(vals)
+        want = [torch.empty_like(vals) for _ in range(world)]
+        dist.all_gather(want, vals)
+        assert got.shape == (world, 3) and torch.equal(got.view(torch.int32), torch.stack(want).view(torch.int32))
+    ints = torch.arange(700, dtype=torch.int32, device="cuda") * (rank + 1) - 5
+    got = b200.all_gather_scalars(ints)
+    assert torch.equal(got, torch.stack([torch.arange(700, dtype=torch.int32, device="cuda") * (r + 1) - 5 for r in range(world)]))
+    # interleaves with SyncBN exchanges of the same communicator
+    bn = b200.B200SyncBatchNorm(8).cuda()
+    y = bn(torch.randn(4, 8, 3, 3, device="cuda"))
+    got = b200.all_gather_scalars(y.detach().float().sum().view(1))
+    assert got.shape == (world, 1) and bool(torch.isfinite(got).all())
+    stats_comm = b200.comm.stats_communicator(None)
+    stats_comm.check_error()
+    with __import__("pytest").raises(ValueError):
+        stats_comm.all_gather_scalars(torch.zeros(2, 2, device="cuda"))
+    dist.barrier()
+    dist.destroy_process_group()
+    return "ok"
+
+
+def test_all_gather_scalars_two_ranks():
+    assert TorchDistributor(num_processes=2).run(_w_gather_scalars) == "ok"
+
+
 def test_checkpoint_round_trip_two_ranks():
     assert TorchDistributor(num_processes=2).run(_w_checkpoint) == "ok"
 
