@@ -35,7 +35,10 @@ def golden():
 
 @pytest.fixture(scope="session", autouse=True)
 def _built_library():
-    """Compile libb200dp.so and the two host shims if they are missing or older than their sources
-    (nvcc cross-compiles without a GPU); a no-op when __graft_entry__.build() has already run."""
+    """Compile libb200dp.so and the two host shims when one of them is MISSING (a fresh checkout: built
+    files are git-ignored; nvcc cross-compiles without a GPU).  Files that exist are used as they are —
+    bringing them up to date is __graft_entry__.build()'s job, and a test run on the GPU box must exercise
+    exactly the binaries that were shipped to it."""
     from dbx_distributed_pytorch_examples_b200 import _lib
-    _lib.build()
+    if not (os.path.exists(_lib.LIB_PATH) and os.path.exists(_lib._fast_path()) and os.path.exists(_lib._autograd_path())):
+        _lib.build()
