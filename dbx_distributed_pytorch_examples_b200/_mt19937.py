@@ -105,7 +105,7 @@ def _peek_uint32(generator, count: int):
     return gen, saved, take_uint32(gen, count)
 
 
-def resized_crop_flip_draws(n: int, height: int, width: int, scale=(0.08, 1.0), ratio=(3.0 / 4.0, 4.0 / 3.0),
+def resized_crop_flip_draws(n: int, height, width, scale=(0.08, 1.0), ratio=(3.0 / 4.0, 4.0 / 3.0),
                             flip_p: float = 0.5, generator=None) -> np.ndarray:
     """int32 [n, 5] = (i, j, h, w, flip): n sequential ``RandomResizedCrop.get_params`` +
     ``RandomHorizontalFlip`` draws (TV/transforms/transforms.py:929-970, :720) from one stream.
@@ -115,9 +115,13 @@ def resized_crop_flip_draws(n: int, height: int, width: int, scale=(0.08, 1.0), 
     the flip consumes one.  ATen's float uniform is ``(word & (2**24-1)) * 2**-24`` in double,
     then ``* (to - from) + from`` (to/from rounded to float32), rounded to float32.  The number
     of words used depends on the data, so a block is read ahead, walked, and the generator
-    is then advanced by exactly what the walk consumed.
+    is then advanced by exactly what the walk consumed.  ``height`` / ``width`` are the image size:
+    one pair for the whole batch, or one value per sample (ragged images in a common slab).
     """
-    area = height * width
+    heights = [int(height)] * n if np.ndim(height) == 0 else [int(v) for v in height]
+    widths = [int(width)] * n if np.ndim(width) == 0 else [int(v) for v in width]
+    if len(heights) != n or len(widths) != n:
+        raise ValueError("per-sample heights / widths must have one entry per sample")
     log_ratio = torch.log(torch.tensor(ratio))  # float32, as torchvision builds it
     s0, s1 = np.float32(scale[0]), np.float32(scale[1])
     r0, r1 = np.float32(float(log_ratio[0])), np.float32(float(log_ratio[1]))
@@ -136,6 +140,8 @@ def resized_crop_flip_draws(n: int, height: int, width: int, scale=(0.08, 1.0), 
             if p + 23 > block:  # worst case: 10 tries + flip
                 ok = False
                 break
+            height, width = heights[k], widths[k]
+            area = height * width
             done = False
             for _ in range(10):
                 target_area = area * as_scale[p]

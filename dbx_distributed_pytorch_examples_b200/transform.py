@@ -20,6 +20,7 @@ from __future__ import annotations
 import ctypes
 from typing import Optional, Sequence
 
+import numpy as np
 import torch
 
 from . import _lib, _mt19937
@@ -144,9 +145,15 @@ def draw_resized_crop_flip_params(n: int, src_hw, scale=(0.08, 1.0), ratio=(3.0 
     """int32 [n, 5] = (i, j, h, w, flip) per sample: ``RandomResizedCrop.get_params``
     (TV/transforms/transforms.py:929-970: up to 10 tries of a uniform area fraction and a
     log-uniform aspect ratio, then two randint, else the central-crop fallback) followed by
-    the flip draw (:720), in that order per sample, from one generator stream."""
-    draws = _mt19937.resized_crop_flip_draws(n, int(src_hw[0]), int(src_hw[1]), tuple(scale), tuple(ratio),
-                                             flip_p, generator)
+    the flip draw (:720), in that order per sample, from one generator stream.  ``src_hw`` is
+    ``(height, width)`` of every image, or an int array ``[n, 2]`` with one size per sample."""
+    hw = np.asarray(src_hw)
+    if hw.ndim == 2:
+        if hw.shape != (n, 2):
+            raise ValueError("per-sample sizes must have shape [n, 2]")
+        draws = _mt19937.resized_crop_flip_draws(n, hw[:, 0], hw[:, 1], tuple(scale), tuple(ratio), flip_p, generator)
+    else:
+        draws = _mt19937.resized_crop_flip_draws(n, int(hw[0]), int(hw[1]), tuple(scale), tuple(ratio), flip_p, generator)
     return torch.from_numpy(draws)
 
 
@@ -155,11 +162,12 @@ def _draw_resized_crop_flip_params_loop(n: int, src_hw, scale=(0.08, 1.0), ratio
     """The literal per-sample torch calls torchvision makes; kept as the check of the replica."""
     import math
 
-    height, width = int(src_hw[0]), int(src_hw[1])
-    area = height * width
+    hw = np.asarray(src_hw)
     log_ratio = torch.log(torch.tensor(ratio))
     out = torch.empty((n, 5), dtype=torch.int32)
     for k in range(n):
+        height, width = (int(hw[k, 0]), int(hw[k, 1])) if hw.ndim == 2 else (int(hw[0]), int(hw[1]))
+        area = height * width
         for _ in range(10):
             target_area = area * torch.empty(1).uniform_(scale[0], scale[1], generator=generator).item()
             aspect = torch.exp(torch.empty(1).uniform_(log_ratio[0], log_ratio[1], generator=generator)).item()
@@ -216,15 +224,20 @@ class ResizeBatchTransform:
         self.last_params = None  # int32 [B,5] on the host
 
     def draw(self, B: int, src_hw, generator=None) -> torch.Tensor:
+        """int32 [B, 5] boxes and flips.  ``src_hw``: ``(height, width)`` of every image, or ``[B, 2]`` sizes of
+        ragged images (each stored in the top-left corner of its slab)."""
         if self.random_resized_crop:
             return draw_resized_crop_flip_params(B, src_hw, self.scale, self.ratio, self.flip_p, generator)
-        flips = draw_crop_flip_params(B, src_hw, src_hw, 0, self.flip_p, generator)[:, 2]
+        flips = draw_crop_flip_params(B, (1, 1), (1, 1), 0, self.flip_p, generator)[:, 2]  # one rand(1) per sample
         out = torch.zeros((B, 5), dtype=torch.int32)
-        out[:, 2], out[:, 3], out[:, 4] = int(src_hw[0]), int(src_hw[1]), flips
+        hw = torch.as_tensor(np.asarray(src_hw), dtype=torch.int32)
+        out[:, 2], out[:, 3], out[:, 4] = (hw[:, 0], hw[:, 1], flips) if hw.dim() == 2 else (int(hw[0]), int(hw[1]), flips)
         return out
 
     def __call__(self, batch: torch.Tensor, *, generator: Optional[torch.Generator] = None,
-                 params: Optional[torch.Tensor] = None) -> torch.Tensor:
+                 params: Optional[torch.Tensor] = None, sizes=None) -> torch.Tensor:
+        """``sizes``: optional ``[B, 2]`` (height, width) of ragged images, each in the top-left corner of its
+        ``[Hs, Ws]`` slab; the boxes are then drawn per image size, as torchvision does per PIL image."""
         if batch.dtype != torch.uint8 or batch.dim() != 4 or batch.shape[-1] != 3:
             raise ValueError("expected a uint8 tensor of shape [B, H, W, 3]")
         if not batch.is_contiguous():
@@ -232,7 +245,13 @@ class ResizeBatchTransform:
         B, Hs, Ws, _ = batch.shape
         H, W = self.size
         if params is None:
-            params = self.draw(B, (Hs, Ws), generator)
+            if sizes is not None:
+                hw = np.asarray(sizes)
+                if hw.shape != (B, 2) or (hw < 1).any() or (hw[:, 0] > Hs).any() or (hw[:, 1] > Ws).any():
+                    raise ValueError("sizes must be [B, 2] with 1 <= height <= Hs and 1 <= width <= Ws")
+                params = self.draw(B, hw, generator)
+            else:
+                params = self.draw(B, (Hs, Ws), generator)
         elif params.dtype != torch.int32 or tuple(params.shape) != (B, 5) or params.is_cuda:
             raise ValueError("params must be a host int32 tensor of shape [B, 5]")
         self.last_params = params

@@ -58,3 +58,33 @@ def test_resized_crop_draws_match_torchvision_golden(golden):
     torch.manual_seed(int(g["seed"]))
     got = T.draw_resized_crop_flip_params(len(g["src"]), g["src"].shape[1:3])
     assert np.array_equal(got.numpy(), g["params"])
+
+
+def test_ragged_image_sizes_draw_like_torchvision_per_image():
+    """Per-sample image sizes (ragged ImageNet-style images in a common slab): the boxes are what torchvision
+    draws when it is handed the images one by one."""
+    from PIL import Image
+    import torchvision.transforms as TV
+    rng = np.random.default_rng(9)
+    sizes = np.stack([rng.integers(20, 300, 40), rng.integers(20, 300, 40)], axis=1)
+    torch.manual_seed(21)
+    want = []
+    for h, w in sizes:
+        i, j, hh, ww = TV.RandomResizedCrop.get_params(Image.new("RGB", (int(w), int(h))), [0.08, 1.0], [3 / 4, 4 / 3])
+        want.append((i, j, hh, ww, int(bool(torch.rand(1) < 0.5))))
+    torch.manual_seed(21)
+    got = T.draw_resized_crop_flip_params(len(sizes), sizes)
+    assert np.array_equal(got.numpy(), np.array(want, dtype=np.int32))
+    assert torch.equal(T._draw_resized_crop_flip_params_loop(5, sizes[:5], generator=torch.Generator().manual_seed(3)),
+                       T.draw_resized_crop_flip_params(5, sizes[:5], generator=torch.Generator().manual_seed(3)))
+    # plain Resize of ragged images: the whole image is the box, one flip draw per sample
+    rt = T.ResizeBatchTransform(32, random_resized_crop=False)
+    g1, g2 = torch.Generator().manual_seed(4), torch.Generator().manual_seed(4)
+    p = rt.draw(len(sizes), sizes, g1)
+    flips = [int(bool(torch.rand(1, generator=g2) < 0.5)) for _ in sizes]
+    assert np.array_equal(p[:, :4].numpy(), np.concatenate([np.zeros_like(sizes), sizes], axis=1))
+    assert p[:, 4].tolist() == flips
+    same = rt.draw(3, (48, 64), torch.Generator().manual_seed(1))
+    assert same[:, 2].tolist() == [48] * 3 and same[:, 3].tolist() == [64] * 3
+    with pytest.raises(ValueError):
+        T.draw_resized_crop_flip_params(3, sizes[:2])
