@@ -207,3 +207,28 @@ def test_autograd_extension_loads_and_binds():
         nat.fused_syncbn(torch.randn(4, 8, 3, 3), torch.randn(4, 8, 3, 2), None, None, 0, 0, 1e-5, 0.1, False, 0, 1, False, 0)
     with pytest.raises(RuntimeError, match="float32 and bfloat16"):
         nat.fused_syncbn(torch.randn(4, 8).double(), None, None, None, 0, 0, 1e-5, 0.1, False, 0, 1, False, 0)
+
+
+def test_stem_pooling_module_swap():
+    """fuse_bn_relu puts B200MaxPool2d behind the stem's fused BN + ReLU (setup/resnet18.py:37,58) for the geometry
+    the kernel handles, leaves anything else alone, keeps the state_dict, and has no CPU path."""
+    m = workloads.cifar_resnet18(10)
+    keys = list(m.state_dict())
+    m = b200.fuse_bn_relu(b200.convert_sync_batchnorm(m))
+    assert isinstance(m.maxpool, b200.B200MaxPool2d) and isinstance(m.maxpool, nn.MaxPool2d)
+    assert (m.maxpool.kernel_size, m.maxpool.stride, m.maxpool.padding) == (3, 2, 1)
+    assert list(m.state_dict()) == keys
+    assert b200.pool.supported(nn.MaxPool2d(2)) and b200.pool.supported(nn.MaxPool2d((3, 3), (2, 2), (1, 1)))
+    for odd in (nn.MaxPool2d(3, 2, 1, ceil_mode=True), nn.MaxPool2d(3, 2, 1, dilation=2), nn.MaxPool2d(5, 2, 2),
+                nn.MaxPool2d((3, 2)), nn.MaxPool2d(3, 2, 1, return_indices=True)):
+        assert not b200.pool.supported(odd)
+    with pytest.raises(NotImplementedError):
+        b200.B200MaxPool2d(3, 2, 1, ceil_mode=True)
+    with pytest.raises(ValueError, match="no CPU path"):
+        m.maxpool(torch.zeros(1, 8, 8, 8))
+    lib = _lib.lib()
+    assert lib.b200dp_maxpool_fwd(None, None, None, 0, 1, 8, 8, 8, 4, 2, 1, None) == -2      # window > 3
+    assert lib.b200dp_maxpool_bwd(None, None, None, 1, 1, 8, 8, 12, 3, 2, 1, None) == -2     # C % 8 (bf16)
+    assert lib.b200dp_maxpool_fwd(None, None, None, 0, 1, 8, 8, 8, 3, 2, 1, None) == -1      # null pointers
+    assert lib.b200dp_resized_crop_u8_bf16(None, -1, 8, 8, None, 8, 8, None, None, None, None) == -1
+    assert lib.b200dp_comm_all_gather32(None, None, 1, None, None) == -1
