@@ -68,13 +68,24 @@ class ShardedBatchSampler:
 
 
 class PinnedImageDataset:
-    """Raw uint8 NHWC images and labels held in page-locked host memory."""
+    """Raw uint8 NHWC images and labels held in page-locked host memory.
 
-    def __init__(self, images_u8: torch.Tensor, labels: torch.Tensor, pin: bool = True):
+    ``sizes`` (optional, int ``[N, 2]`` = height, width): images of different sizes, each stored in the
+    top-left corner of its ``[H, W]`` slab; ``batches`` then yields ``(images, labels, sizes)`` and the sizes go
+    to ``ResizeBatchTransform(...)(images, sizes=sizes)``."""
+
+    def __init__(self, images_u8: torch.Tensor, labels: torch.Tensor, pin: bool = True, sizes=None):
         if images_u8.dtype != torch.uint8 or images_u8.dim() != 4 or images_u8.shape[-1] != 3:
             raise ValueError("expected uint8 images of shape [N, H, W, 3]")
         if len(labels) != len(images_u8):
             raise ValueError("images and labels differ in length")
+        self.sizes = None
+        if sizes is not None:
+            sz = torch.as_tensor(sizes).to(torch.int32).contiguous()
+            if tuple(sz.shape) != (len(images_u8), 2) or bool((sz < 1).any()) or \
+                    bool((sz[:, 0] > images_u8.shape[1]).any()) or bool((sz[:, 1] > images_u8.shape[2]).any()):
+                raise ValueError("sizes must be [N, 2] with 1 <= height <= H and 1 <= width <= W")
+            self.sizes = sz
         can_pin = pin and torch.cuda.is_available()
         self.images = images_u8.contiguous().pin_memory() if can_pin else images_u8.contiguous()
         self.labels = labels.to(torch.int64).contiguous()
@@ -99,7 +110,10 @@ class PinnedImageDataset:
             torch.index_select(self.images, 0, idx, out=slot[0])
             torch.index_select(self.labels, 0, idx, out=slot[1])
             k += 1
-            yield slot
+            if self.sizes is None:
+                yield slot
+            else:
+                yield slot[0], slot[1], torch.index_select(self.sizes, 0, idx)  # host metadata, not copied to the GPU
 
 
 class DeviceFeeder:
@@ -111,13 +125,13 @@ class DeviceFeeder:
         self.copy_stream = torch.cuda.Stream(device=self.device)
 
     def _start_copy(self, batch):
-        images, labels = batch
+        images, labels, *rest = batch  # anything after the labels (image sizes) stays on the host
         with torch.cuda.stream(self.copy_stream):
             d_img = images.to(self.device, non_blocking=True)
             d_lab = labels.to(self.device, non_blocking=True)
             done = torch.cuda.Event()
             done.record(self.copy_stream)
-        return d_img, d_lab, done
+        return d_img, d_lab, done, tuple(rest)
 
     def __iter__(self):
         it = iter(self.host_batches)
@@ -126,7 +140,7 @@ class DeviceFeeder:
         except StopIteration:
             return
         while pending is not None:
-            d_img, d_lab, done = pending
+            d_img, d_lab, done, rest = pending
             # This copy was issued a whole step ago, so the wait is free; it guarantees that the
             # pinned staging slot of this (and every older) batch may be refilled by next(it).
             done.synchronize()
@@ -139,7 +153,7 @@ class DeviceFeeder:
             # the copy stream allocated these; tell the allocator the compute stream uses them
             d_img.record_stream(cur)
             d_lab.record_stream(cur)
-            yield d_img, d_lab
+            yield (d_img, d_lab) + rest
 
 
 class LossReader:

@@ -232,3 +232,24 @@ def test_stem_pooling_module_swap():
     assert lib.b200dp_maxpool_fwd(None, None, None, 0, 1, 8, 8, 8, 3, 2, 1, None) == -1      # null pointers
     assert lib.b200dp_resized_crop_u8_bf16(None, -1, 8, 8, None, 8, 8, None, None, None, None) == -1
     assert lib.b200dp_comm_all_gather32(None, None, 1, None, None) == -1
+
+
+def test_pinned_dataset_with_ragged_sizes():
+    from dbx_distributed_pytorch_examples_b200.feed import PinnedImageDataset, ShardedBatchSampler
+    imgs = torch.randint(0, 256, (10, 12, 16, 3), dtype=torch.uint8)
+    labels = torch.arange(10)
+    sizes = torch.stack([torch.arange(3, 13), torch.arange(7, 17)], dim=1)
+    ds = PinnedImageDataset(imgs, labels, sizes=sizes)
+    sampler = ShardedBatchSampler(len(ds), 4, rank=0, world=1, shuffle=False, drop_last=False)
+    seen = 0
+    for data, target, hw in ds.batches(sampler):
+        idx = target.tolist()
+        assert torch.equal(data, imgs[idx]) and hw.dtype == torch.int32 and torch.equal(hw, sizes[idx].int())
+        seen += len(idx)
+    assert seen == 10
+    plain = PinnedImageDataset(imgs, labels)
+    assert all(len(b) == 2 for b in plain.batches(sampler))
+    with pytest.raises(ValueError):
+        PinnedImageDataset(imgs, labels, sizes=sizes + 10)      # larger than the slab
+    with pytest.raises(ValueError):
+        PinnedImageDataset(imgs, labels, sizes=sizes[:3])
