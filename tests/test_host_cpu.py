@@ -253,3 +253,33 @@ def test_pinned_dataset_with_ragged_sizes():
         PinnedImageDataset(imgs, labels, sizes=sizes + 10)      # larger than the slab
     with pytest.raises(ValueError):
         PinnedImageDataset(imgs, labels, sizes=sizes[:3])
+
+
+def test_bucket_plan_invariants_property():
+    """Random parameter lists: the plan tiles the arena, keeps 16-byte alignment per parameter and whole vectors
+    per rank slice, and groups parameters like torch's Reducer (up to the padding)."""
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=60, deadline=None)
+    @given(st.lists(st.integers(1, 3_000_000), min_size=1, max_size=40), st.sampled_from([1, 2, 4, 8]),
+           st.sampled_from([2, 4]), st.sampled_from([1, 5, 25]))
+    def check(numels, world, esize, cap_mb):
+        offsets, buckets, total = ddp.plan_buckets(numels, esize, world, cap_mb * 1024 * 1024)
+        assert len(offsets) == len(numels) and all(o % 8 == 0 for o in offsets)
+        assert buckets[0][0] == 0 and sum(n for _, n, _, _ in buckets) == total
+        nxt_start, nxt_param = 0, 0
+        for (s, n, p0, p1) in buckets:
+            assert s == nxt_start and p0 == nxt_param and p1 > p0 and n % (8 * world) == 0
+            for k in range(p0, p1):
+                assert s <= offsets[k] and offsets[k] + numels[k] <= s + n
+            for k in range(p0, p1 - 1):
+                assert offsets[k] + numels[k] <= offsets[k + 1]
+            nxt_start, nxt_param = s + n, p1
+        assert nxt_param == len(numels)
+        if world == 1:
+            # the padding to 8 elements can only make a bucket close earlier than torch's byte count would
+            ours = [list(range(p0, p1)) for _, _, p0, p1 in buckets]
+            padded = [(n + 7) // 8 * 8 * esize for n in numels]
+            assert ours == ddp_ref.bucket_assignment(padded, cap=cap_mb * 1024 * 1024)
+
+    check()
