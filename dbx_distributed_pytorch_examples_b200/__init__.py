@@ -20,7 +20,7 @@ from .comm import Communicator, all_gather_scalars  # noqa: F401
 from .ddp import B200DDP, prepare_model  # noqa: F401
 from .distributor import DeepspeedTorchDistributor, TorchDistributor  # noqa: F401
 from .feed import DeviceFeeder, LossReader, PinnedImageDataset, ShardedBatchSampler  # noqa: F401
-from .fusion import fuse_bn_relu  # noqa: F401
+from .fusion import fuse_bn_relu, unfuse_bn_relu  # noqa: F401
 from .syncbn import B200SyncBatchNorm, convert_sync_batchnorm  # noqa: F401
 from .pool import B200MaxPool2d  # noqa: F401
 from .transform import (BatchTransform, ResizeBatchTransform, draw_crop_flip_params,  # noqa: F401

@@ -160,6 +160,7 @@ _VP = c_void_p
 _SIGNATURES = {
     # name: (restype, argtypes)
     "b200dp_version": (c_int, []),
+    "b200dp_kernel_launches": (ctypes.c_ulonglong, []),
     "b200dp_error_string": (c_char_p, [c_int]),
     "b200dp_augment_u8_bf16": (c_int, [_VP, c_int, c_int, c_int, _VP, c_int, c_int, c_int,
                                        POINTER(c_float), POINTER(c_float), _VP, _VP]),
@@ -194,6 +195,9 @@ _SIGNATURES = {
     "b200dp_comm_barrier": (c_int, [_VP, _VP]),
     "b200dp_comm_all_gather32": (c_int, [_VP, _VP, c_int, _VP, _VP]),
     "b200dp_comm_error": (c_int, [_VP]),
+    "b200dp_comm_error_async": (c_int, [_VP, _VP, _VP]),
+    "b200dp_bn_one_kernel": (c_int, [c_int, c_int64, c_int, c_int]),
+    "b200dp_bn_set_one_kernel_limits": (c_int, [c_int, c_int, c_int]),
     "b200dp_bucket_pack": (c_int, [POINTER(_VP), POINTER(c_int64), POINTER(c_int64), c_int, _VP,
                                    c_int, c_float, _VP]),
     "b200dp_allreduce_update": (c_int, [_VP, c_size_t, c_int, c_size_t, c_int, c_int64, c_int64,

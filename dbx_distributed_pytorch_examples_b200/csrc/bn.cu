@@ -82,24 +82,31 @@ Grid2 plan_grid_clustered(int64_t M, int C, int max_clusters) {
   return g;
 }
 
-// cudaOccupancyMaxActiveClusters for a kernel of this file, asked once per device.
+// cudaOccupancyMaxActiveClusters for a kernel of this file with clusters of `cs` CTAs, asked once per
+// (kernel, device, cluster size).  Forward runs on the caller's thread and backward on autograd's, so the
+// small cache is guarded.  Returns 0 when the runtime cannot place such a cluster at all.
+std::mutex g_occ_mutex;
 template <typename KernelT>
-int max_active_clusters(KernelT kernel) {
-  struct Entry { const void* fn; int dev; int n; };
-  static Entry table[256];  // (kernel, device) -> clusters; racing writers store the same value
+int max_active_clusters(KernelT kernel, int cs = kCluster) {
+  struct Entry { const void* fn; int dev; int cs; int n; };
+  static Entry table[512];
   static int used = 0;
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess) return 64;
   const void* key = reinterpret_cast<const void*>(kernel);
+  std::lock_guard<std::mutex> lock(g_occ_mutex);
   for (int i = 0; i < used; ++i)
-    if (table[i].fn == key && table[i].dev == dev) return table[i].n;
+    if (table[i].fn == key && table[i].dev == dev && table[i].cs == cs) return table[i].n;
+  if (cs > 8) {  // clusters of more than 8 CTAs are an opt-in per kernel
+    if (cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) cudaGetLastError();
+  }
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(kCluster * B200DP_NUM_SMS, 1, 1);
+  cfg.gridDim = dim3(cs * B200DP_NUM_SMS, 1, 1);
   cfg.blockDim = dim3(kT, 1, 1);
   cfg.dynamicSmemBytes = 0;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = kCluster;
+  attr[0].val.clusterDim.x = cs;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
@@ -107,11 +114,12 @@ int max_active_clusters(KernelT kernel) {
   int n = 0;
   if (cudaOccupancyMaxActiveClusters(&n, kernel, &cfg) != cudaSuccess || n <= 0) {
     cudaGetLastError();
-    n = 64;  // conservative: 8 per GPC
+    n = cs == kCluster ? 64 : 0;  // the portable size: be conservative (8 per GPC); larger ones: not available
   }
-  if (used < 256) {
+  if (used < 512) {
     table[used].fn = key;
     table[used].dev = dev;
+    table[used].cs = cs;
     table[used].n = n;
     ++used;
   }
@@ -136,31 +144,61 @@ __device__ __forceinline__ void welford_merge(float& na, float* ma, float* qa, f
   na = n;
 }
 
-// Tree over the 32 row-slots of a CTA.  sm is laid out [k][tid] (conflict free).
+// ---- reduction over the row slots of a CTA ---------------------------------------------------
+// Thread tid owns channel group tid % cvw and row slot tid / cvw (cvw = 16-byte vectors per row chunk:
+// 8 in the two-kernel path, 2/4/8 in the one-kernel path), so the lanes of a warp that share a channel
+// group are cvw apart: log2(32 / cvw) shuffle steps leave the warp's partial in lanes < cvw.
 template <int N, bool WELFORD>
-__device__ __forceinline__ void cta_tree(float* sA, float* sB, float* sN, float& n, float* a,
-                                         float* b) {
-  const int tid = threadIdx.x;
-  const int r = tid / kCV;
+__device__ __forceinline__ void warp_fold(int cvw, float& n, float* a, float* b) {
+  for (int o = 16; o >= cvw; o >>= 1) {
+    float oa[N], ob[N];
+    const float on = WELFORD ? __shfl_down_sync(0xffffffffu, n, o) : 0.f;
 #pragma unroll
-  for (int k = 0; k < N; ++k) {
-    sA[k * kT + tid] = a[k];
-    sB[k * kT + tid] = b[k];
+    for (int k = 0; k < N; ++k) {
+      oa[k] = __shfl_down_sync(0xffffffffu, a[k], o);
+      ob[k] = __shfl_down_sync(0xffffffffu, b[k], o);
+    }
+    if (WELFORD) {
+      welford_merge<N>(n, a, b, on, oa, ob);
+    } else {
+#pragma unroll
+      for (int k = 0; k < N; ++k) {
+        a[k] += oa[k];
+        b[k] += ob[k];
+      }
+    }
   }
-  if (WELFORD) sN[tid] = n;
+}
+
+// The 8 warp partials meet in shared memory (wp: kT/32 * cvw * (2N+1) floats) and threads tid < cvw
+// fold them in warp order: one barrier instead of the five of a tree over 32 row slots.  On return
+// threads tid < cvw hold the CTA's (n, a[], b[]) for their channel group.
+template <int N, bool WELFORD>
+__device__ __forceinline__ void cta_fold(int cvw, float* wp, float& n, float* a, float* b) {
+  constexpr int W = 2 * N + 1;
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  warp_fold<N, WELFORD>(cvw, n, a, b);
+  if (lane < cvw) {
+    float* d = wp + (w * cvw + lane) * W;
+#pragma unroll
+    for (int k = 0; k < N; ++k) {
+      d[k] = a[k];
+      d[N + k] = b[k];
+    }
+    d[2 * N] = n;
+  }
   __syncthreads();
-  for (int s = kRows / 2; s > 0; s >>= 1) {
-    if (r < s) {
-      const int o = tid + s * kCV;
+  if (tid < cvw) {
+    for (int q = 1; q < kT / 32; ++q) {
+      const float* src = wp + (q * cvw + tid) * W;
       float oa[N], ob[N];
 #pragma unroll
       for (int k = 0; k < N; ++k) {
-        oa[k] = sA[k * kT + o];
-        ob[k] = sB[k * kT + o];
+        oa[k] = src[k];
+        ob[k] = src[N + k];
       }
       if (WELFORD) {
-        welford_merge<N>(n, a, b, sN[o], oa, ob);
-        sN[tid] = n;
+        welford_merge<N>(n, a, b, src[2 * N], oa, ob);
       } else {
 #pragma unroll
         for (int k = 0; k < N; ++k) {
@@ -168,14 +206,14 @@ __device__ __forceinline__ void cta_tree(float* sA, float* sB, float* sN, float&
           b[k] += ob[k];
         }
       }
-#pragma unroll
-      for (int k = 0; k < N; ++k) {
-        sA[k * kT + tid] = a[k];
-        sB[k * kT + tid] = b[k];
-      }
     }
-    __syncthreads();
   }
+}
+
+// Same interface as the tree it replaces: sA is the CTA's reduction scratch (>= 8*8*(2N+1) floats).
+template <int N, bool WELFORD>
+__device__ __forceinline__ void cta_tree(float* sA, float*, float*, float& n, float* a, float* b) {
+  cta_fold<N, WELFORD>(kCV, sA, n, a, b);
 }
 
 // After the CTA tree, threads with r == 0 hold the CTA's (n, a[], b[]) for their
@@ -290,53 +328,64 @@ __device__ __forceinline__ bool grid_merge(void* scratch, int C, int chbase, boo
   return true;
 }
 
-// Store this rank's chunk of an exchange vector into every rank's slot as LL words
-// {value, seq} (see b200dp_sync_area).  Called by the whole electing CTA; `a`/`b`/`cnt` are
-// valid in threads with r == 0.
-template <int N>
-__device__ __forceinline__ void push_chunk(const b200dp_peers& P, uint32_t seq, int C, int c0,
-                                           bool chan_ok, const float* a, const float* b,
-                                           float cnt) {
-  const int tid = threadIdx.x, r = tid / kCV;
+// ---- cross-rank exchange of one channel chunk ---------------------------------------------------
+// A chunk is `cw` consecutive channels starting at `cb` (cw <= kChunkMax).  Its exchange vector is
+// a[cw] | b[cw] | cnt, staged in shared memory as stage[0..cw) | stage[cw..2cw) | stage[2cw].  In a rank's
+// slot (b200dp_sync_area::bn_ll[slot][rank]) a[c] sits at word c, b[c] at C + c, and the count at
+// 2*MAX_CHANNELS + cb/64 (every chunk that covers part of a 64-channel group writes the same value
+// there), so ranks whose kernels cut the channels into different chunks still understand each other.
+// Words are LL words {value, seq}; two adjacent ones travel as one 16-byte store / load.
+constexpr int kChunkMax = kCV * 8;                 // channels per chunk at most (bf16, 8 vectors)
+constexpr int kXrStride = 2 * kChunkMax + 4;       // floats per rank in the gathered copy
+
+// The whole CTA stores the staged vector into every rank's slot: world * (cw + 1) stores spread over
+// its 256 threads (before: 8 threads issuing 17 scalar stores per peer, back to back).
+__device__ __forceinline__ void push_chunk(const b200dp_peers& P, uint32_t seq, int C, int cb, int cw,
+                                           const float* stage) {
   const int slot = seq % B200DP_XCHG_SLOTS;
-  const int by = blockIdx.y;
-  if (r == 0 && chan_ok) {
-    for (int p = 0; p < P.world; ++p) {
-      uint2* d = P.sync[p]->bn_ll[slot][P.rank];
-#pragma unroll
-      for (int k = 0; k < N; ++k) {
-        st_ll(d + c0 + k, a[k], seq);
-        st_ll(d + C + c0 + k, b[k], seq);
-      }
-      if (tid == 0) st_ll(d + 2 * B200DP_BN_MAX_CHANNELS + by, cnt, seq);
+  const int valid = (C - cb < cw) ? C - cb : cw;  // multiple of 4: whole pairs
+  const int pairs = valid >> 1;
+  const int units = 2 * pairs + 1;
+  for (int u = threadIdx.x; u < P.world * units; u += kT) {
+    const int p = u / units;
+    int j = u - p * units;
+    uint2* d = P.sync[p]->bn_ll[slot][P.rank];
+    if (j < pairs) {
+      st_ll2(d + cb + 2 * j, stage[2 * j], stage[2 * j + 1], seq);
+    } else if (j < 2 * pairs) {
+      j -= pairs;
+      st_ll2(d + C + cb + 2 * j, stage[cw + 2 * j], stage[cw + 2 * j + 1], seq);
+    } else {
+      st_ll(d + 2 * B200DP_BN_MAX_CHANNELS + (cb >> 6), stage[2 * cw], seq);
     }
   }
 }
 
-// world*kCV threads poll the ranks' LL words of this chunk side by side and put the values
-// into shared memory (xr[rank][cv][2N+1 (+pad)]); the kCV coefficient threads then merge
-// from shared memory in rank order.
-constexpr int kXrStride = 20;  // floats per (rank, cv): 2*8 + 1 used, padded to a multiple of 4
-template <int N>
-__device__ __forceinline__ void wait_and_gather(const b200dp_peers& P, uint32_t seq, int C, float* xr) {
+// The whole CTA polls the ranks' words of this chunk in its own sync area (the peers stored them there)
+// and leaves them in shared memory: xr[rank * kXrStride + ...] = a[cw] | b[cw] | cnt.  At most
+// ceil(world * (cw + 1) / 256) polls per thread, side by side (before: 17 one after the other).
+__device__ __forceinline__ void wait_and_gather(const b200dp_peers& P, uint32_t seq, int C, int cb, int cw,
+                                                float* xr) {
   const int slot = seq % B200DP_XCHG_SLOTS;
-  const int tid = threadIdx.x;
-  if (tid < P.world * kCV) {
-    const int p = tid / kCV, cv = tid % kCV;
-    const int c0 = blockIdx.y * (kCV * N) + cv * N;
-    if (c0 < C) {
-      const uint2* d = P.sync[P.rank]->bn_ll[slot][p];
-      float* o = xr + (p * kCV + cv) * kXrStride;
-      bool ok = true;
-#pragma unroll
-      for (int k = 0; k < N; ++k) {
-        ok &= ld_ll(d + c0 + k, seq, o + k);
-        ok &= ld_ll(d + C + c0 + k, seq, o + N + k);
-      }
-      ok &= ld_ll(d + 2 * B200DP_BN_MAX_CHANNELS + blockIdx.y, seq, o + 2 * N);
-      if (!ok) atomicExch(&P.sync[P.rank]->error, 1u);
+  const int valid = (C - cb < cw) ? C - cb : cw;
+  const int pairs = valid >> 1;
+  const int units = 2 * pairs + 1;
+  bool ok = true;
+  for (int u = threadIdx.x; u < P.world * units; u += kT) {
+    const int p = u / units;
+    int j = u - p * units;
+    const uint2* d = P.sync[P.rank]->bn_ll[slot][p];
+    float* o = xr + p * kXrStride;
+    if (j < pairs) {
+      ok &= ld_ll2(d + cb + 2 * j, seq, o + 2 * j, o + 2 * j + 1, P.timeout);
+    } else if (j < 2 * pairs) {
+      j -= pairs;
+      ok &= ld_ll2(d + C + cb + 2 * j, seq, o + cw + 2 * j, o + cw + 2 * j + 1, P.timeout);
+    } else {
+      ok &= ld_ll(d + 2 * B200DP_BN_MAX_CHANNELS + (cb >> 6), seq, o + 2 * cw, P.timeout);
     }
   }
+  if (!ok) atomicExch(&P.sync[P.rank]->error, 1u);
   __syncthreads();
 }
 
@@ -484,7 +533,7 @@ constexpr int kDefaultBnOrder = 10;  // the apply kernels walk against the reduc
 template <typename T>
 __global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kT, kOccFwd)
 bn_stats_kernel(const T* __restrict__ x, int64_t M, int C, void* scratch, float* stats_local,
-                b200dp_peers P, uint32_t seq, int rev) {
+                const __grid_constant__ b200dp_peers P, uint32_t seq, int rev) {
   constexpr int N = Vec<T>::N;
   using Ring = RowRing<kDepthStats, 1, false>;
   constexpr int kTreeBytes = (2 * N * kT + kT) * 4;
@@ -566,7 +615,20 @@ bn_stats_kernel(const T* __restrict__ x, int64_t M, int C, void* scratch, float*
     }
     if (tid == 0 && blockIdx.y == 0) stats_local[2 * C] = n;
   }
-  if (P.world > 1) push_chunk<N>(P, seq, C, c0, chan_ok, mean, m2, n);
+  if (P.world > 1) {
+    constexpr int cw = kCV * N;
+    __syncthreads();  // the fold above is done with sA everywhere
+    if (r == 0) {
+#pragma unroll
+      for (int k = 0; k < N; ++k) {
+        sA[cv * N + k] = mean[k];
+        sA[cw + cv * N + k] = m2[k];
+      }
+      if (tid == 0) sA[2 * cw] = n;
+    }
+    __syncthreads();
+    push_chunk(P, seq, C, blockIdx.y * cw, cw, sA);
+  }
 }
 
 // ============================ forward: normalise =============================
@@ -598,10 +660,8 @@ struct FwdArgs {
 // threads (one 16-byte channel group each), and handed to the other 31 rows of threads
 // through shared memory: a small layer gives every thread only a handful of rows, and
 // 256 threads each redoing the divisions and square roots cost more than the rows.
-constexpr int kChunkMax = kCV * 8;  // channels per chunk at most (bf16)
-
 template <typename T, bool RELU, bool RES>
-__global__ void __launch_bounds__(kT, kOccFwd) bn_fwd_apply_kernel(FwdArgs A, b200dp_peers P, uint32_t seq) {
+__global__ void __launch_bounds__(kT, kOccFwd) bn_fwd_apply_kernel(const __grid_constant__ FwdArgs A, const __grid_constant__ b200dp_peers P, uint32_t seq) {
   constexpr int N = Vec<T>::N;
   using Ring = RowRing<RES ? 4 : 8, RES ? 2 : 1, true>;
   __shared__ __align__(16) unsigned char smem[Ring::kBytes];
@@ -631,8 +691,9 @@ __global__ void __launch_bounds__(kT, kOccFwd) bn_fwd_apply_kernel(FwdArgs A, b2
   if (A.batches_tracked && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) *A.batches_tracked += 1;
   pdl_wait();  // statistics of the producer kernel are complete and visible from here on
 
-  __shared__ __align__(16) float xr[B200DP_MAX_WORLD * kCV * kXrStride];
-  if (!A.given_mean && P.world > 1) wait_and_gather<N>(P, seq, C, xr);
+  __shared__ __align__(16) float xr[B200DP_MAX_WORLD * kXrStride];
+  constexpr int cw = kCV * N;
+  if (!A.given_mean && P.world > 1) wait_and_gather(P, seq, C, blockIdx.y * cw, cw, xr);
   if (tid < kCV && chan_ok) {  // r == 0: this thread's c0 is the group it publishes
     float mean[N], a[N], b[N];
     if (A.given_mean) {
@@ -649,8 +710,8 @@ __global__ void __launch_bounds__(kT, kOccFwd) bn_fwd_apply_kernel(FwdArgs A, b2
       for (int k = 0; k < N; ++k) mean[k] = m2[k] = 0.f;
       if (P.world > 1) {
         for (int p = 0; p < P.world; ++p) {  // rank order: every rank computes identical statistics
-          const float* o = xr + (p * kCV + cv) * kXrStride;
-          welford_merge<N>(n, mean, m2, o[2 * N], o, o + N);
+          const float* o = xr + p * kXrStride;
+          welford_merge<N>(n, mean, m2, o[2 * cw], o + cv * N, o + cw + cv * N);
         }
       } else {
         n = ld_cg_f32(A.stats_local + 2 * C);
@@ -741,7 +802,7 @@ __global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kT, kOccFwd)
 bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T* __restrict__ yo,
                      int64_t M, int C, const float* save_mean, const float* save_invstd,
                      const float* weight, const float* bias, void* scratch, float* sums_local,
-                     float* grad_weight, float* grad_bias, b200dp_peers P, uint32_t seq, int rev) {
+                     float* grad_weight, float* grad_bias, const __grid_constant__ b200dp_peers P, uint32_t seq, int rev) {
   constexpr int N = Vec<T>::N;
   using Ring = RowRing<RELU >= 2 ? 3 : 4, RELU >= 2 ? 3 : 2, false, RELU == 3>;  // 32 or 36 KiB (static smem limit 48 KiB)
   constexpr int kTreeBytes = 2 * N * kT * 4;
@@ -848,7 +909,20 @@ bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T*
       if (grad_weight) grad_weight[c0 + k] = s2[k] * save_invstd[c0 + k];
     }
   }
-  if (P.world > 1) push_chunk<N>(P, seq, C, c0, chan_ok, s1, s2, 0.f);
+  if (P.world > 1) {
+    constexpr int cw = kCV * N;
+    __syncthreads();
+    if (r == 0) {
+#pragma unroll
+      for (int k = 0; k < N; ++k) {
+        sA[cv * N + k] = s1[k];
+        sA[cw + cv * N + k] = s2[k];
+      }
+      if (tid == 0) sA[2 * cw] = 0.f;
+    }
+    __syncthreads();
+    push_chunk(P, seq, C, blockIdx.y * cw, cw, sA);
+  }
 }
 
 // ============================== backward: apply ==============================
@@ -870,7 +944,7 @@ struct BwdArgs {
 };
 
 template <typename T, int RELU, bool DRES>
-__global__ void __launch_bounds__(kT, kOccBwd) bn_bwd_apply_kernel(BwdArgs A, b200dp_peers P, uint32_t seq) {
+__global__ void __launch_bounds__(kT, kOccBwd) bn_bwd_apply_kernel(const __grid_constant__ BwdArgs A, const __grid_constant__ b200dp_peers P, uint32_t seq) {
   constexpr int N = Vec<T>::N;
   using Ring = RowRing<RELU >= 2 ? 3 : 4, RELU >= 2 ? 3 : 2, true, RELU == 3>;
   __shared__ __align__(16) unsigned char smem[Ring::kBytes];
@@ -901,19 +975,20 @@ __global__ void __launch_bounds__(kT, kOccBwd) bn_bwd_apply_kernel(BwdArgs A, b2
   ring.prime(nrows, ptrs);  // in flight during the flag wait and the prologue
   pdl_wait();
 
-  __shared__ __align__(16) float xr[B200DP_MAX_WORLD * kCV * kXrStride];
-  if (P.world > 1) wait_and_gather<N>(P, seq, C, xr);
+  __shared__ __align__(16) float xr[B200DP_MAX_WORLD * kXrStride];
+  constexpr int cw = kCV * N;
+  if (P.world > 1) wait_and_gather(P, seq, C, blockIdx.y * cw, cw, xr);
   if (tid < kCV && chan_ok) {
     float s1[N], s2[N];
 #pragma unroll
     for (int k = 0; k < N; ++k) s1[k] = s2[k] = 0.f;
     if (P.world > 1) {
       for (int p = 0; p < P.world; ++p) {
-        const float* o = xr + (p * kCV + cv) * kXrStride;
+        const float* o = xr + p * kXrStride;
 #pragma unroll
         for (int k = 0; k < N; ++k) {
-          s1[k] += o[k];
-          s2[k] += o[N + k];
+          s1[k] += o[cv * N + k];
+          s2[k] += o[cw + cv * N + k];
         }
       }
     } else {
@@ -999,6 +1074,536 @@ __global__ void __launch_bounds__(kT, kOccBwd) bn_bwd_apply_kernel(BwdArgs A, b2
   ring.run(nrows, ptrs, proc);
 }
 
+// ==================== one kernel per direction for layers that fit the L2 ====================
+// The two-kernel path pays a second launch, a second prologue and a grid-wide hand-over (partials in
+// global memory, a ticket, a last CTA) per layer and direction: ~15 us that do not shrink with the layer,
+// and 40 of ResNet-50's 53 BN layers are small enough for that to be most of their time.  Here ONE
+// thread-block cluster owns a channel chunk for ALL rows: it streams the rows once for the statistics
+// (or the backward sums), folds them over its CTAs through distributed shared memory — hardware
+// co-schedules the CTAs of a cluster, so that wait cannot starve whatever else runs on the GPU, which a
+// grid-wide spin could — exchanges them across ranks, and streams the rows a second time to apply,
+// this time out of the L2 they were just read into.  Chunks are narrow (2, 4 or 8 sixteen-byte vectors
+// per row instead of 8) so that even C = 128 gives enough clusters to fill the GPU.
+constexpr int kFusedMaxCS = 16;      // CTAs per cluster (16 is an opt-in size; 8 when the device refuses it)
+constexpr int kFusedMaxGroups = 64;  // cluster size x vectors per row chunk at most (bounds the DSMEM exchange buffer)
+
+struct FusedGeom {
+  int cvw;   // 16-byte vectors per row chunk (2, 4, 8)
+  int cs;    // cluster size = row splits
+  int rev2;  // second pass walks the rows last -> first (most recently read first)
+};
+
+// Every CTA of the cluster hands its partial (threads tid < cvw) to every CTA, itself included; after the
+// cluster barrier each folds the cs partials in CTA order, so all of them hold bit-identical results.
+// mine: smem [cvw * W]; xchg: smem [kFusedMaxGroups * W], written remotely.
+template <int N, bool WELFORD>
+__device__ __forceinline__ void cluster_fold(int cvw, int cs, float* mine, float* xchg, float& n, float* a,
+                                             float* b, cg::cluster_group::arrival_token&& started) {
+  constexpr int W = 2 * N + 1;
+  const int tid = threadIdx.x;
+  cg::cluster_group cluster = cg::this_cluster();
+  const unsigned rank = cluster.block_rank();
+  if (tid < cvw) {
+    float* d = mine + tid * W;
+#pragma unroll
+    for (int k = 0; k < N; ++k) {
+      d[k] = a[k];
+      d[N + k] = b[k];
+    }
+    d[2 * N] = n;
+  }
+  __syncthreads();
+  cluster.barrier_wait(std::move(started));  // every CTA of the cluster has started: its shared memory exists
+  const int per = cvw * W;
+  for (int it = tid; it < cs * per; it += kT) {
+    const int q = it / per, e = it - q * per;
+    float* dst = cluster.map_shared_rank(xchg + rank * per + e, q);
+    *dst = mine[e];
+  }
+  cluster.sync();  // release / acquire at cluster scope
+  if (tid < cvw) {
+    n = 0.f;
+#pragma unroll
+    for (int k = 0; k < N; ++k) a[k] = b[k] = 0.f;
+    for (int q = 0; q < cs; ++q) {
+      const float* src = xchg + q * per + tid * W;
+      float oa[N], ob[N];
+#pragma unroll
+      for (int k = 0; k < N; ++k) {
+        oa[k] = src[k];
+        ob[k] = src[N + k];
+      }
+      if (WELFORD) {
+        welford_merge<N>(n, a, b, src[2 * N], oa, ob);
+      } else {
+#pragma unroll
+        for (int k = 0; k < N; ++k) {
+          a[k] += oa[k];
+          b[k] += ob[k];
+        }
+      }
+    }
+  }
+}
+
+struct FusedRows {
+  int64_t first, step;
+  int count;
+};
+__device__ __forceinline__ FusedRows fused_rows(int64_t M, int r, int rp, int cs) {
+  FusedRows rr;
+  rr.step = (int64_t)cs * rp;
+  rr.first = (int64_t)blockIdx.x * rp + r;
+  rr.count = rr.first < M ? (int)((M - rr.first + rr.step - 1) / rr.step) : 0;
+  return rr;
+}
+
+constexpr int kFusedRingBytes = 36 * 1024;  // the largest ring any phase uses (3 streams x 3 deep)
+
+template <typename T, bool RELU, bool RES>
+__global__ void __launch_bounds__(kT, kOccFwd)
+bn_fwd_fused_kernel(const __grid_constant__ FwdArgs A, const FusedGeom G, const __grid_constant__ b200dp_peers P,
+                    uint32_t seq) {
+  constexpr int N = Vec<T>::N;
+  constexpr int W = 2 * N + 1;
+  using Ring1 = RowRing<8, 1, false>;
+  using Ring2 = RowRing<RES ? 4 : 8, RES ? 2 : 1, true>;
+  __shared__ __align__(16) unsigned char smem[Ring1::kBytes];  // rings, then the warp partials of the fold
+  __shared__ __align__(16) float xchg[kFusedMaxGroups * W];
+  __shared__ __align__(16) float mine[2 * kChunkMax + 8];       // partial for the cluster, then the exchange stage
+  __shared__ __align__(16) float coef[3][kChunkMax];
+  __shared__ __align__(16) float xr[B200DP_MAX_WORLD * kXrStride];
+  static_assert(Ring2::kBytes <= Ring1::kBytes, "ring");
+  const int tid = threadIdx.x;
+  const int cvw = G.cvw, cs = G.cs, rp = kT / cvw;
+  const int cv = tid % cvw, r = tid / cvw;
+  const int C = A.C;
+  const int cw = cvw * N, cb = blockIdx.y * cw;
+  const int c0 = cb + cv * N;
+  const bool chan_ok = c0 < C;
+  auto started = cg::this_cluster().barrier_arrive();
+
+  const T* xb = static_cast<const T*>(A.x);
+  const T* rb = static_cast<const T*>(A.res);
+  T* yb = static_cast<T*>(A.y);
+  const FusedRows rr = fused_rows(A.M, r, rp, cs);
+  const int nrows = chan_ok ? rr.count : 0;
+  const int64_t rstep = rr.step * C;
+  const int64_t off_first = rr.first * C + c0;
+
+  // ---- pass 1: statistics of this CTA's rows ----
+  float n = 0.f, mean[N], m2[N];
+#pragma unroll
+  for (int k = 0; k < N; ++k) mean[k] = m2[k] = 0.f;
+  pdl_wait();
+  if (A.batches_tracked && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) *A.batches_tracked += 1;
+  {
+    auto ptrs = [&](int k, const void*& p0, const void*& p1, const void*& p2) {
+      p0 = xb + off_first + k * rstep;
+      p1 = p2 = nullptr;
+    };
+    auto proc = [&](int, const uint4& v, const uint4&, const uint4&) {
+      if constexpr (is_bf16<T>::value) {
+#pragma unroll
+        for (int k = 0; k < N; ++k) {
+          const uint16_t h = vec_half(v, k);
+          mean[k] = add_bf16_f32(h, mean[k]);
+          m2[k] = fma_bf16_f32(h, h, m2[k]);
+        }
+      } else {
+        float f[N];
+        Vec<T>::unpack(v, f);
+        n += 1.f;
+        const float rn = __frcp_rn(n);
+#pragma unroll
+        for (int k = 0; k < N; ++k) {
+          const float d = f[k] - mean[k];
+          mean[k] = fmaf(d, rn, mean[k]);
+          m2[k] = fmaf(d, f[k] - mean[k], m2[k]);
+        }
+      }
+    };
+    Ring1 ring;
+    ring.init(smem);
+    ring.prime(nrows, ptrs);
+    ring.run(nrows, ptrs, proc);
+    if constexpr (is_bf16<T>::value) {
+      n = (float)nrows;
+      if (nrows > 0) {
+        const float rn = 1.0f / n;
+#pragma unroll
+        for (int k = 0; k < N; ++k) {
+          const float s = mean[k];
+          mean[k] = s * rn;
+          m2[k] = fmaxf(fmaf(-s, mean[k], m2[k]), 0.f);
+        }
+      }
+    }
+  }
+  __syncthreads();  // rings drained: the fold may use the memory
+  cta_fold<N, true>(cvw, reinterpret_cast<float*>(smem), n, mean, m2);
+  cluster_fold<N, true>(cvw, cs, mine, xchg, n, mean, m2, std::move(started));
+  // threads tid < cvw of every CTA now hold this rank's (n, mean, M2) of their channel group
+
+  // second pass: start the rows flying before the coefficients are worked out
+  const bool rev = G.rev2 != 0;
+  const int64_t off2 = off_first + (rev ? (int64_t)(rr.count - 1) * rstep : 0);
+  const int64_t step2 = rev ? -rstep : rstep;
+  auto ptrs2 = [&](int k, const void*& p0, const void*& p1, const void*& p2) {
+    p0 = xb + off2 + k * step2;
+    p1 = RES ? (const void*)(rb + off2 + k * step2) : nullptr;
+    p2 = nullptr;
+  };
+  __syncthreads();  // the fold is done with smem
+  Ring2 ring2;
+  ring2.init(smem);
+  ring2.prime(nrows, ptrs2);
+
+  const bool leader = blockIdx.x == 0;
+  if (leader && tid < cvw && chan_ok) {
+    float* so = const_cast<float*>(A.stats_local);  // an output here (the apply kernel only reads it)
+#pragma unroll
+    for (int k = 0; k < N; ++k) {
+      so[c0 + k] = mean[k];
+      so[C + c0 + k] = m2[k];
+    }
+    if (tid == 0 && blockIdx.y == 0) so[2 * C] = n;
+  }
+  if (P.world > 1) {
+    if (leader) {
+      if (tid < cvw) {
+#pragma unroll
+        for (int k = 0; k < N; ++k) {
+          mine[cv * N + k] = mean[k];
+          mine[cw + cv * N + k] = m2[k];
+        }
+        if (tid == 0) mine[2 * cw] = n;
+      }
+      __syncthreads();
+      push_chunk(P, seq, C, cb, cw, mine);
+    }
+    wait_and_gather(P, seq, C, cb, cw, xr);
+  }
+  if (tid < cvw && chan_ok) {
+    if (P.world > 1) {
+      n = 0.f;
+#pragma unroll
+      for (int k = 0; k < N; ++k) mean[k] = m2[k] = 0.f;
+      for (int p = 0; p < P.world; ++p) {
+        const float* o = xr + p * kXrStride;
+        welford_merge<N>(n, mean, m2, o[2 * cw], o + cv * N, o + cw + cv * N);
+      }
+    }
+    const float inv_n = n > 0.f ? 1.0f / n : 0.f;
+    const float inv_nm1 = n > 1.f ? 1.0f / (n - 1.f) : 0.f;
+    float a[N], b[N];
+#pragma unroll
+    for (int k = 0; k < N; ++k) {
+      const float var = m2[k] * inv_n;
+      const float invstd = 1.0f / sqrtf(var + A.eps);
+      a[k] = invstd * (A.weight ? A.weight[c0 + k] : 1.f);
+      b[k] = A.bias ? A.bias[c0 + k] : 0.f;
+      if (leader) {
+        A.save_mean[c0 + k] = mean[k];
+        A.save_invstd[c0 + k] = invstd;
+        if (A.running_mean)
+          A.running_mean[c0 + k] = (1.f - A.momentum) * A.running_mean[c0 + k] + A.momentum * mean[k];
+        if (A.running_var)
+          A.running_var[c0 + k] = (1.f - A.momentum) * A.running_var[c0 + k] + A.momentum * (m2[k] * inv_nm1);
+      }
+      mean[k] = -mean[k];
+    }
+    if (leader && tid == 0 && blockIdx.y == 0) A.save_count[0] = n;
+    sts_vec<N>(&coef[0][cv * N], mean);
+    sts_vec<N>(&coef[1][cv * N], a);
+    sts_vec<N>(&coef[2][cv * N], b);
+  }
+  __syncthreads();
+  float nmean[N], a[N], b[N];
+  ldg_vec<N>(&coef[0][cv * N], nmean);
+  ldg_vec<N>(&coef[1][cv * N], a);
+  ldg_vec<N>(&coef[2][cv * N], b);
+
+  // ---- pass 2: normalise (+ residual) (+ ReLU) ----
+  auto proc2 = [&](int k, const uint4& vx, const uint4& vr, const uint4&) {
+    float f[N];
+    if constexpr (is_bf16<T>::value) {
+#pragma unroll
+      for (int j = 0; j < N; ++j) {
+        float o = fmaf(add_bf16_f32(vec_half(vx, j), nmean[j]), a[j], b[j]);
+        if (RES) o = add_bf16_f32(vec_half(vr, j), o);
+        f[j] = RELU ? fmaxf(o, 0.f) : o;
+      }
+    } else {
+      float g[N];
+      Vec<T>::unpack(vx, f);
+      if (RES) Vec<T>::unpack(vr, g);
+#pragma unroll
+      for (int j = 0; j < N; ++j) {
+        float o = fmaf(f[j] + nmean[j], a[j], b[j]);
+        if (RES) o += g[j];
+        f[j] = RELU ? fmaxf(o, 0.f) : o;
+      }
+    }
+    const uint4 pk = Vec<T>::pack(f);
+    *reinterpret_cast<uint4*>(yb + off2 + k * step2) = pk;
+    if constexpr (RELU && is_bf16<T>::value) {
+      if (A.maskw) {
+        const uint32_t w[4] = {pk.x, pk.y, pk.z, pk.w};
+        uint32_t bits = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          bits |= ((w[j] & 0xffffu) != 0u ? 1u : 0u) << (2 * j);
+          bits |= ((w[j] >> 16) != 0u ? 1u : 0u) << (2 * j + 1);
+        }
+        A.maskw[(off2 + k * step2) >> 3] = bits;
+      }
+    }
+  };
+  ring2.run(nrows, ptrs2, proc2);
+}
+
+// Backward: sums over the rows, cluster fold, cross-rank exchange, then dx (and d_residual).
+struct BwdFusedArgs {
+  BwdArgs b;
+  float* sums_local;   // out: [2C] this rank's sums (the two-kernel path's contract)
+  float* grad_weight;  // out or NULL
+  float* grad_bias;    // out or NULL
+};
+
+template <typename T, int RELU, bool DRES>
+__global__ void __launch_bounds__(kT, kOccBwd)
+bn_bwd_fused_kernel(const __grid_constant__ BwdFusedArgs F, const FusedGeom G,
+                    const __grid_constant__ b200dp_peers P, uint32_t seq) {
+  constexpr int N = Vec<T>::N;
+  constexpr int W = 2 * N + 1;
+  using Ring1 = RowRing<RELU >= 2 ? 3 : 4, RELU >= 2 ? 3 : 2, false, RELU == 3>;
+  using Ring2 = RowRing<RELU >= 2 ? 3 : 4, RELU >= 2 ? 3 : 2, true, RELU == 3>;
+  __shared__ __align__(16) unsigned char smem[Ring1::kBytes];
+  __shared__ __align__(16) float xchg[kFusedMaxGroups * W];
+  __shared__ __align__(16) float mine[2 * kChunkMax + 8];
+  __shared__ __align__(16) float coef[2][kChunkMax];
+  const BwdArgs& A = F.b;
+  const int tid = threadIdx.x;
+  const int cvw = G.cvw, cs = G.cs, rp = kT / cvw;
+  const int cv = tid % cvw, r = tid / cvw;
+  const int C = A.C;
+  const int cw = cvw * N, cb = blockIdx.y * cw;
+  const int c0 = cb + cv * N;
+  const bool chan_ok = c0 < C;
+  auto started = cg::this_cluster().barrier_arrive();
+
+  const T* dyb = static_cast<const T*>(A.dy);
+  const T* xb = static_cast<const T*>(A.x);
+  const T* yob = static_cast<const T*>(A.yo);
+  T* dxb = static_cast<T*>(A.dx);
+  T* dresb = static_cast<T*>(A.dres);
+  const FusedRows rr = fused_rows(A.M, r, rp, cs);
+  const int nrows = chan_ok ? rr.count : 0;
+  const int64_t rstep = rr.step * C;
+  const int64_t off_first = rr.first * C + c0;
+
+  float s1[N], s2[N];
+#pragma unroll
+  for (int k = 0; k < N; ++k) s1[k] = s2[k] = 0.f;
+  float nmean[N], a[N], b[N];
+#pragma unroll
+  for (int k = 0; k < N; ++k) { nmean[k] = 0.f; a[k] = 1.f; b[k] = 0.f; }
+  pdl_wait();
+  {
+    auto ptrs = [&](int k, const void*& p0, const void*& p1, const void*& p2) {
+      p0 = dyb + off_first + k * rstep;
+      p1 = xb + off_first + k * rstep;
+      p2 = RELU == 2   ? (const void*)(yob + off_first + k * rstep)
+           : RELU == 3 ? (const void*)(reinterpret_cast<const uint32_t*>(yob) + ((off_first + k * rstep) >> 3))
+                       : nullptr;
+    };
+    Ring1 ring;
+    ring.init(smem);
+    ring.prime(nrows, ptrs);
+    if (chan_ok) {
+      float mean[N];
+      ldg_vec<N>(A.save_mean + c0, mean);
+#pragma unroll
+      for (int k = 0; k < N; ++k) nmean[k] = -mean[k];
+      ldg_vec<N>(A.save_invstd + c0, a);
+      if (A.weight) {
+        float w[N];
+        ldg_vec<N>(A.weight + c0, w);
+#pragma unroll
+        for (int k = 0; k < N; ++k) a[k] *= w[k];
+      }
+      if (A.bias) ldg_vec<N>(A.bias + c0, b);
+    }
+    auto proc = [&](int, const uint4& vg, const uint4& vx, const uint4& vy) {
+      if constexpr (is_bf16<T>::value) {
+        uint4 g = vg;
+        if (RELU == 2) {
+          g.x = bf16x2_mul(vg.x, bf16x2_gt0_mask(vy.x));
+          g.y = bf16x2_mul(vg.y, bf16x2_gt0_mask(vy.y));
+          g.z = bf16x2_mul(vg.z, bf16x2_gt0_mask(vy.z));
+          g.w = bf16x2_mul(vg.w, bf16x2_gt0_mask(vy.w));
+        }
+        if (RELU == 3) g = apply_mask_word(vg, vy.x);
+#pragma unroll
+        for (int k = 0; k < N; ++k) {
+          const uint16_t gh = vec_half(g, k), xh = vec_half(vx, k);
+          if (RELU == 1) {
+            const bool on = fmaf(add_bf16_f32(xh, nmean[k]), a[k], b[k]) > 0.f;
+            s1[k] = on ? add_bf16_f32(gh, s1[k]) : s1[k];
+            s2[k] = on ? fma_bf16_f32(gh, xh, s2[k]) : s2[k];
+          } else {
+            s1[k] = add_bf16_f32(gh, s1[k]);
+            s2[k] = fma_bf16_f32(gh, xh, s2[k]);
+          }
+        }
+      } else {
+        float g[N], f[N], o[N];
+        Vec<T>::unpack(vg, g);
+        Vec<T>::unpack(vx, f);
+        if (RELU == 2) Vec<T>::unpack(vy, o);
+#pragma unroll
+        for (int k = 0; k < N; ++k) {
+          const float xm = f[k] + nmean[k];
+          float gk = g[k];
+          if (RELU == 1) gk = fmaf(xm, a[k], b[k]) > 0.f ? gk : 0.f;
+          if (RELU == 2) gk = o[k] > 0.f ? gk : 0.f;
+          s1[k] += gk;
+          s2[k] = fmaf(gk, xm, s2[k]);
+        }
+      }
+    };
+    ring.run(nrows, ptrs, proc);
+    if constexpr (is_bf16<T>::value) {
+#pragma unroll
+      for (int k = 0; k < N; ++k) s2[k] = fmaf(nmean[k], s1[k], s2[k]);
+    }
+  }
+  __syncthreads();
+  float dummy = 0.f;
+  cta_fold<N, false>(cvw, reinterpret_cast<float*>(smem), dummy, s1, s2);
+  cluster_fold<N, false>(cvw, cs, mine, xchg, dummy, s1, s2, std::move(started));
+
+  const bool rev = G.rev2 != 0;
+  const int64_t off2 = off_first + (rev ? (int64_t)(rr.count - 1) * rstep : 0);
+  const int64_t step2 = rev ? -rstep : rstep;
+  auto ptrs2 = [&](int k, const void*& p0, const void*& p1, const void*& p2) {
+    p0 = dyb + off2 + k * step2;
+    p1 = xb + off2 + k * step2;
+    p2 = RELU == 2   ? (const void*)(yob + off2 + k * step2)
+         : RELU == 3 ? (const void*)(reinterpret_cast<const uint32_t*>(yob) + ((off2 + k * step2) >> 3))
+                     : nullptr;
+  };
+  __syncthreads();
+  Ring2 ring2;
+  ring2.init(smem);
+  ring2.prime(nrows, ptrs2);
+
+  const bool leader = blockIdx.x == 0;
+  if (leader && tid < cvw && chan_ok) {
+#pragma unroll
+    for (int k = 0; k < N; ++k) {
+      F.sums_local[c0 + k] = s1[k];
+      F.sums_local[C + c0 + k] = s2[k];
+      if (F.grad_bias) F.grad_bias[c0 + k] = s1[k];
+      if (F.grad_weight) F.grad_weight[c0 + k] = s2[k] * A.save_invstd[c0 + k];
+    }
+  }
+  __shared__ __align__(16) float xr[B200DP_MAX_WORLD * kXrStride];
+  if (P.world > 1) {
+    if (leader) {
+      if (tid < cvw) {
+#pragma unroll
+        for (int k = 0; k < N; ++k) {
+          mine[cv * N + k] = s1[k];
+          mine[cw + cv * N + k] = s2[k];
+        }
+        if (tid == 0) mine[2 * cw] = 0.f;
+      }
+      __syncthreads();
+      push_chunk(P, seq, C, cb, cw, mine);
+    }
+    wait_and_gather(P, seq, C, cb, cw, xr);
+  }
+  if (tid < cvw && chan_ok) {
+    if (P.world > 1) {
+#pragma unroll
+      for (int k = 0; k < N; ++k) s1[k] = s2[k] = 0.f;
+      for (int p = 0; p < P.world; ++p) {
+        const float* o = xr + p * kXrStride;
+#pragma unroll
+        for (int k = 0; k < N; ++k) {
+          s1[k] += o[cv * N + k];
+          s2[k] += o[cw + cv * N + k];
+        }
+      }
+    }
+    const float cnt = ld_cg_f32(A.save_count);
+    const float inv_cnt = cnt > 0.f ? 1.0f / cnt : 0.f;
+    float nmdy[N], nkx[N];
+#pragma unroll
+    for (int k = 0; k < N; ++k) {
+      const float invstd = A.save_invstd[c0 + k];
+      nmdy[k] = -(s1[k] * inv_cnt);
+      nkx[k] = -(s2[k] * inv_cnt * invstd * invstd);
+    }
+    sts_vec<N>(&coef[0][cv * N], nmdy);
+    sts_vec<N>(&coef[1][cv * N], nkx);
+  }
+  __syncthreads();
+  float nmdy[N], nkx[N];
+  ldg_vec<N>(&coef[0][cv * N], nmdy);
+  ldg_vec<N>(&coef[1][cv * N], nkx);
+
+  auto proc2 = [&](int k, const uint4& vg, const uint4& vx, const uint4& vy) {
+    float f[N];
+    if constexpr (is_bf16<T>::value) {
+      uint4 g = vg;
+      if (RELU == 2) {
+        g.x = bf16x2_mul(vg.x, bf16x2_gt0_mask(vy.x));
+        g.y = bf16x2_mul(vg.y, bf16x2_gt0_mask(vy.y));
+        g.z = bf16x2_mul(vg.z, bf16x2_gt0_mask(vy.z));
+        g.w = bf16x2_mul(vg.w, bf16x2_gt0_mask(vy.w));
+      }
+      if (RELU == 3) g = apply_mask_word(vg, vy.x);
+      float gm[N];
+#pragma unroll
+      for (int j = 0; j < N; ++j) {
+        const float xm = add_bf16_f32(vec_half(vx, j), nmean[j]);
+        float t = add_bf16_f32(vec_half(g, j), nmdy[j]);
+        if (RELU == 1) {
+          const bool on = fmaf(xm, a[j], b[j]) > 0.f;
+          t = on ? t : nmdy[j];
+          if (DRES) gm[j] = on ? add_bf16_f32(vec_half(g, j), 0.f) : 0.f;
+        }
+        f[j] = fmaf(xm, nkx[j], t) * a[j];
+      }
+      *reinterpret_cast<uint4*>(dxb + off2 + k * step2) = Vec<T>::pack(f);
+      if (DRES) {
+        if (RELU == 1) *reinterpret_cast<uint4*>(dresb + off2 + k * step2) = Vec<T>::pack(gm);
+        else *reinterpret_cast<uint4*>(dresb + off2 + k * step2) = g;
+      }
+    } else {
+      float g[N], o[N];
+      Vec<T>::unpack(vg, g);
+      Vec<T>::unpack(vx, f);
+      if (RELU == 2) Vec<T>::unpack(vy, o);
+#pragma unroll
+      for (int j = 0; j < N; ++j) {
+        const float xm = f[j] + nmean[j];
+        float gk = g[j];
+        if (RELU == 1) gk = fmaf(xm, a[j], b[j]) > 0.f ? gk : 0.f;
+        if (RELU == 2) gk = o[j] > 0.f ? gk : 0.f;
+        g[j] = gk;
+        f[j] = fmaf(xm, nkx[j], gk + nmdy[j]) * a[j];
+      }
+      *reinterpret_cast<uint4*>(dxb + off2 + k * step2) = Vec<T>::pack(f);
+      if (DRES) *reinterpret_cast<uint4*>(dresb + off2 + k * step2) = Vec<T>::pack(g);
+    }
+  };
+  ring2.run(nrows, ptrs2, proc2);
+}
+
 // Row traversal order of the four training kernels: bit 0 statistics, bit 1 forward apply,
 // bit 2 backward reduce, bit 3 backward apply; a set bit walks the rows from the last to the
 // first.  A kernel that runs against the direction of the one before it starts on the rows
@@ -1037,6 +1642,133 @@ cudaError_t launch_ex(void (*kernel)(KArgs...), dim3 grid, cudaStream_t s, bool 
   cfg.attrs = attr;
   cfg.numAttrs = pdl ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
+// ---- which layers take the one-kernel path, and with what geometry ----
+// B200DP_BN_FUSED=0 turns it off; B200DP_BN_FUSED_MB / B200DP_BN_FUSED_BWD_MB bound the tensor size
+// (MiB of x; default: what stays in the 126 MB L2 next to the tensors written meanwhile);
+// B200DP_BN_FUSED_CS=8 keeps to the portable cluster size.
+struct FusedCfg {
+  bool on;
+  int64_t fwd_bytes, bwd_bytes;
+  int cs;
+};
+FusedCfg& fused_cfg() {  // read from the environment once; b200dp_bn_set_one_kernel_limits() may change it later
+  static FusedCfg cfg = [] {
+    FusedCfg c;
+    const char* e = getenv("B200DP_BN_FUSED");
+    c.on = !(e && e[0] == '0');
+    e = getenv("B200DP_BN_FUSED_MB");
+    c.fwd_bytes = (int64_t)(e && e[0] ? atoi(e) : 56) << 20;
+    e = getenv("B200DP_BN_FUSED_BWD_MB");
+    c.bwd_bytes = (int64_t)(e && e[0] ? atoi(e) : 40) << 20;
+    e = getenv("B200DP_BN_FUSED_CS");
+    c.cs = (e && atoi(e) == 8) ? 8 : kFusedMaxCS;
+    return c;
+  }();
+  return cfg;
+}
+
+struct FusedPlan {
+  bool ok;
+  FusedGeom g;
+  int chunks;
+};
+
+// Candidates (vectors per row chunk, cluster size): wide chunks use whole 128-byte lines, narrow ones
+// give more clusters.  Take the widest that still yields >= 256 CTAs, else the one with the most CTAs.
+template <typename T, typename KernelT>
+FusedPlan plan_fused(KernelT kernel, int64_t M, int C, int64_t limit_bytes) {
+  FusedPlan pl;
+  pl.ok = false;
+  const FusedCfg& cfg = fused_cfg();
+  if (!cfg.on || limit_bytes <= 0 || M * C * (int64_t)sizeof(T) > limit_bytes) return pl;
+  const int big = (cfg.cs == kFusedMaxCS && max_active_clusters(kernel, kFusedMaxCS) > 0) ? kFusedMaxCS : 8;
+  const int nvec = C / Vec<T>::N;
+  const int cand[3][2] = {{8, 8}, {4, big}, {2, big}};
+  int best = -1, best_ctas = 0;
+  for (int i = 0; i < 3; ++i) {
+    const int chunks = (nvec + cand[i][0] - 1) / cand[i][0];
+    const int ctas = chunks * cand[i][1];
+    if (ctas >= 256) { best = i; break; }
+    if (ctas > best_ctas) { best = i; best_ctas = ctas; }
+  }
+  pl.g.cvw = cand[best][0];
+  pl.g.cs = cand[best][1];
+  pl.g.rev2 = 1;
+  pl.chunks = (nvec + pl.g.cvw - 1) / pl.g.cvw;
+  pl.ok = true;
+  return pl;
+}
+
+template <typename... KArgs, typename... Args>
+cudaError_t launch_cluster(void (*kernel)(KArgs...), int cs, int chunks, cudaStream_t s, bool pdl, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(cs, chunks, 1);
+  cfg.blockDim = dim3(kT, 1, 1);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = cs;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 2 : 1;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
+constexpr int kNotFused = -1000;  // internal: the layer takes the two-kernel path
+
+template <typename T>
+int launch_fwd_fused(const FwdArgs& A, bool relu, const b200dp_peers& P, uint32_t seq, cudaStream_t s) {
+  const bool res = A.res != nullptr;
+  cudaError_t e;
+#define B200DP_FWD_FUSED(RELU, RES)                                                              \
+  do {                                                                                           \
+    const FusedPlan pl = plan_fused<T>(bn_fwd_fused_kernel<T, RELU, RES>, A.M, A.C, fused_cfg().fwd_bytes); \
+    if (!pl.ok) return kNotFused;                                                                \
+    e = launch_cluster(bn_fwd_fused_kernel<T, RELU, RES>, pl.g.cs, pl.chunks, s, pdl_first(), A, pl.g, P, seq); \
+  } while (0)
+  if (relu && res) B200DP_FWD_FUSED(true, true);
+  else if (relu) B200DP_FWD_FUSED(true, false);
+  else if (res) B200DP_FWD_FUSED(false, true);
+  else B200DP_FWD_FUSED(false, false);
+#undef B200DP_FWD_FUSED
+  if (e != cudaSuccess) return (int)e;
+  B200DP_LAUNCH_CHECK();
+  return B200DP_OK;
+}
+
+template <typename T>
+int launch_bwd_fused(const BwdFusedArgs& F, int relu, const b200dp_peers& P, uint32_t seq, cudaStream_t s) {
+  const bool dres = F.b.dres != nullptr;
+  cudaError_t e = cudaSuccess;
+#define B200DP_BWD_FUSED(R, D)                                                                   \
+  do {                                                                                           \
+    const FusedPlan pl = plan_fused<T>(bn_bwd_fused_kernel<T, R, D>, F.b.M, F.b.C, fused_cfg().bwd_bytes); \
+    if (!pl.ok) return kNotFused;                                                                \
+    e = launch_cluster(bn_bwd_fused_kernel<T, R, D>, pl.g.cs, pl.chunks, s, pdl_first(), F, pl.g, P, seq); \
+  } while (0)
+#define B200DP_BWD_FUSED_R(R)            \
+  do {                                   \
+    if (dres) B200DP_BWD_FUSED(R, true); \
+    else B200DP_BWD_FUSED(R, false);     \
+  } while (0)
+  if (relu == 0) B200DP_BWD_FUSED_R(0);
+  else if (relu == 1) B200DP_BWD_FUSED_R(1);
+  else if (relu == 2) B200DP_BWD_FUSED_R(2);
+  else {
+    if constexpr (is_bf16<T>::value) B200DP_BWD_FUSED_R(3);
+    else return B200DP_EUNSUPPORTED;
+  }
+#undef B200DP_BWD_FUSED_R
+#undef B200DP_BWD_FUSED
+  if (e != cudaSuccess) return (int)e;
+  B200DP_LAUNCH_CHECK();
+  return B200DP_OK;
 }
 
 // ================================ host side ==================================
@@ -1131,20 +1863,23 @@ extern "C" int b200dp_bn_fwd_stats_noalloc(const void* x, int dtype, int64_t M, 
   void* scratch = nullptr;
   if ((rc = bn_static_scratch(&scratch))) return rc;
   cudaStream_t s = (cudaStream_t)stream;
-  // The array is shared by every call and keeps what the last one left in it.  Only the
-  // "last CTA" tickets have to start at zero; partials and counts are written before they
-  // are read.  Clearing them here also recovers from a call that was cut short.
-  B200DP_CUDA_TRY(cudaMemsetAsync((char*)scratch + kScratchTickets, 0, kScratchCounts - kScratchTickets, s));
   const b200dp_peers P = b200dp_make_peers(nullptr);
   Grid2 g;
   if (dtype == B200DP_BF16) {
     g = plan_grid_clustered<__nv_bfloat16>(M, C, max_active_clusters(bn_stats_kernel<__nv_bfloat16>));
     if ((size_t)g.gx * g.gy * kCV * Vec<__nv_bfloat16>::N > (size_t)kMaxPartials) return B200DP_ETOOBIG;
-    bn_stats_kernel<__nv_bfloat16><<<dim3(g.gx, g.gy), kT, 0, s>>>(
-        static_cast<const __nv_bfloat16*>(x), M, C, scratch, stats_local, P, 0, 0);
   } else {
     g = plan_grid_clustered<float>(M, C, max_active_clusters(bn_stats_kernel<float>));
     if ((size_t)g.gx * g.gy * kCV * Vec<float>::N > (size_t)kMaxPartials) return B200DP_ETOOBIG;
+  }
+  // The array is shared by every call and keeps what the last one left in it.  Only the
+  // "last CTA" tickets have to start at zero; partials and counts are written before they
+  // are read.  Clearing them here also recovers from a call that was cut short.
+  B200DP_CUDA_TRY(cudaMemsetAsync((char*)scratch + kScratchTickets, 0, kScratchCounts - kScratchTickets, s));
+  if (dtype == B200DP_BF16) {
+    bn_stats_kernel<__nv_bfloat16><<<dim3(g.gx, g.gy), kT, 0, s>>>(
+        static_cast<const __nv_bfloat16*>(x), M, C, scratch, stats_local, P, 0, 0);
+  } else {
     bn_stats_kernel<float><<<dim3(g.gx, g.gy), kT, 0, s>>>(static_cast<const float*>(x), M, C,
                                                            scratch, stats_local, P, 0, 0);
   }
@@ -1334,7 +2069,23 @@ extern "C" int b200dp_bn_forward(const void* x, const void* residual, void* y, i
                                  int64_t* num_batches_tracked) {
   if (!save) return B200DP_EINVAL;
   if ((uintptr_t)num_batches_tracked & 7) return B200DP_EALIGN;
-  int rc = b200dp_bn_fwd_stats(x, dtype, M, C, scratch, stats_local, comm, seq, stream);
+  int rc;
+  if (fused_cfg().on) {  // small layer: statistics and normalise in one cluster kernel
+    rc = check_common(x, residual, y, dtype, M, C);
+    if (rc) return rc;
+    if (relu_mask && (dtype != B200DP_BF16 || !relu)) return B200DP_EUNSUPPORTED;
+    if (!stats_local || !scratch) return B200DP_EINVAL;
+    if (M > 0 && !y) return B200DP_EINVAL;
+    if ((rc = check_comm(comm, seq))) return rc;
+    FwdArgs A{x, residual, y, M, C, stats_local, weight, bias, eps, momentum, running_mean,
+              running_var, save, save + C, save + 2 * C, nullptr, nullptr, relu_mask, 0,
+              reinterpret_cast<long long*>(num_batches_tracked)};
+    const b200dp_peers P = b200dp_make_peers(comm);
+    rc = dtype == B200DP_BF16 ? launch_fwd_fused<__nv_bfloat16>(A, relu != 0, P, seq, (cudaStream_t)stream)
+                              : launch_fwd_fused<float>(A, relu != 0, P, seq, (cudaStream_t)stream);
+    if (rc != kNotFused) return rc;
+  }
+  rc = b200dp_bn_fwd_stats(x, dtype, M, C, scratch, stats_local, comm, seq, stream);
   if (rc) return rc;
   t_pdl_next = true;  // the normalise kernel may start while the statistics kernel finishes its tail
   rc = fwd_apply_impl(x, residual, y, dtype, M, C, stats_local, weight, bias, eps, momentum,
@@ -1350,12 +2101,52 @@ extern "C" int b200dp_bn_backward(const void* dy, const void* x, const void* y_o
                                   float* sums_local, float* grad_weight, float* grad_bias,
                                   b200dp_comm* comm, uint32_t seq, b200dp_stream_t stream) {
   if (!save) return B200DP_EINVAL;
-  int rc = b200dp_bn_bwd_reduce(dy, x, y_out, dtype, M, C, save, save + C, weight, bias, relu, scratch,
-                                sums_local, grad_weight, grad_bias, comm, seq, stream);
+  int rc;
+  if (fused_cfg().on) {  // small layer: sums and apply in one cluster kernel
+    rc = check_common(dy, x, dx, dtype, M, C);
+    if (rc) return rc;
+    if (!aligned16(y_out) || !aligned16(d_residual)) return B200DP_EALIGN;
+    if (relu < 0 || relu > 3) return B200DP_EINVAL;
+    if (relu == 3 && dtype != B200DP_BF16) return B200DP_EUNSUPPORTED;
+    if (M > 0 && (!x || !dx || (relu >= 2 && !y_out))) return B200DP_EINVAL;
+    if (!scratch || !sums_local) return B200DP_EINVAL;
+    if ((rc = check_comm(comm, seq))) return rc;
+    BwdFusedArgs F{{dy, x, y_out, dx, d_residual, M, C, save, save + C, weight, bias, sums_local, save + 2 * C, 0},
+                   sums_local, grad_weight, grad_bias};
+    const b200dp_peers P = b200dp_make_peers(comm);
+    rc = dtype == B200DP_BF16 ? launch_bwd_fused<__nv_bfloat16>(F, relu, P, seq, (cudaStream_t)stream)
+                              : launch_bwd_fused<float>(F, relu, P, seq, (cudaStream_t)stream);
+    if (rc != kNotFused) return rc;
+  }
+  rc = b200dp_bn_bwd_reduce(dy, x, y_out, dtype, M, C, save, save + C, weight, bias, relu, scratch,
+                            sums_local, grad_weight, grad_bias, comm, seq, stream);
   if (rc) return rc;
   t_pdl_next = true;
   rc = b200dp_bn_bwd_apply(dy, x, y_out, dx, d_residual, dtype, M, C, save, save + C, weight, bias,
                            sums_local, save + 2 * C, relu, comm, seq, stream);
   t_pdl_next = false;
   return rc;
+}
+
+// 1 when b200dp_bn_forward (backward != 0: b200dp_bn_backward) runs this layer as ONE kernel (a thread-block
+// cluster per channel chunk, tensors that fit the L2), 0 when it issues the statistics / reduce kernel and
+// the apply kernel.  For callers that time or count launches; the results are the same either way.
+// Limits of the one-kernel path at run time (tests and A/B measurements; not thread-safe against calls in
+// flight on other host threads): tensor size bounds in MiB for the forward / backward (0 = never, < 0 =
+// leave as it is) and the cluster size (8 or 16, anything else = leave as it is).
+extern "C" int b200dp_bn_set_one_kernel_limits(int fwd_mb, int bwd_mb, int cluster_size) {
+  FusedCfg& cfg = fused_cfg();
+  if (fwd_mb >= 0) cfg.fwd_bytes = (int64_t)fwd_mb << 20;
+  if (bwd_mb >= 0) cfg.bwd_bytes = (int64_t)bwd_mb << 20;
+  if (cluster_size == 8 || cluster_size == kFusedMaxCS) cfg.cs = cluster_size;
+  cfg.on = cfg.fwd_bytes > 0 || cfg.bwd_bytes > 0;
+  return B200DP_OK;
+}
+
+extern "C" int b200dp_bn_one_kernel(int dtype, int64_t M, int C, int backward) {
+  const FusedCfg& cfg = fused_cfg();
+  if (!cfg.on || (dtype != B200DP_F32 && dtype != B200DP_BF16)) return 0;
+  const int64_t bytes = M * C * (dtype == B200DP_BF16 ? 2 : 4);
+  const int64_t limit = backward ? cfg.bwd_bytes : cfg.fwd_bytes;
+  return (limit > 0 && bytes <= limit) ? 1 : 0;
 }

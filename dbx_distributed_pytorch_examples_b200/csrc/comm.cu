@@ -7,6 +7,7 @@
 //   sync  (b200dp_sync_area)  flags + SyncBN exchange slots, zero-filled once
 // Flags only ever grow (they hold exchange sequence numbers), so nothing is
 // reset between steps and a late reader can never see a "cleared" flag.
+#include <atomic>
 #include <new>
 #include <string.h>
 
@@ -16,19 +17,19 @@ namespace {
 
 using namespace b200dp;
 
-__global__ void barrier_kernel(b200dp_peers P, uint32_t seq) {
+__global__ void barrier_kernel(const __grid_constant__ b200dp_peers P, uint32_t seq) {
   const int t = threadIdx.x;
   if (t < P.world) {
     __threadfence_system();
     st_release_sys(&P.sync[t]->barrier[P.rank], seq);
-    if (!wait_flag(&P.sync[P.rank]->barrier[t], seq)) atomicExch(&P.sync[P.rank]->error, 1u);
+    if (!wait_flag(&P.sync[P.rank]->barrier[t], seq, P.timeout)) atomicExch(&P.sync[P.rank]->error, 1u);
   }
 }
 
 // All-gather of k 32-bit words per rank through the SyncBN exchange slots ("LL" words: {payload, seq}
 // written with one 8-byte store into every peer's slot, polled by the reader): one kernel, one NVLink
 // traversal, no separate flag.  Thread idx handles (rank idx / k, word idx % k) in both phases.
-__global__ void gather32_kernel(b200dp_peers P, uint32_t seq, const uint32_t* __restrict__ in, int k,
+__global__ void gather32_kernel(const __grid_constant__ b200dp_peers P, uint32_t seq, const uint32_t* __restrict__ in, int k,
                                 uint32_t* __restrict__ out) {
   const int slot = seq % B200DP_XCHG_SLOTS;
   const int total = k * P.world;
@@ -39,7 +40,7 @@ __global__ void gather32_kernel(b200dp_peers P, uint32_t seq, const uint32_t* __
   for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
     const int src = idx / k, j = idx - src * k;
     float v;
-    if (!ld_ll(&P.sync[P.rank]->bn_ll[slot][src][j], seq, &v)) atomicExch(&P.sync[P.rank]->error, 1u);
+    if (!ld_ll(&P.sync[P.rank]->bn_ll[slot][src][j], seq, &v, P.timeout)) atomicExch(&P.sync[P.rank]->error, 1u);
     out[idx] = __float_as_uint(v);
   }
 }
@@ -54,6 +55,12 @@ static_assert(sizeof(ExportBlob) == B200DP_COMM_HANDLE_BYTES, "export blob size"
 }  // namespace
 
 extern "C" int b200dp_version(void) { return B200DP_VERSION; }
+
+namespace {
+std::atomic<unsigned long long> g_launches{0};
+}
+extern "C" unsigned long long b200dp_count_launch(void) { return ++g_launches; }
+extern "C" unsigned long long b200dp_kernel_launches(void) { return g_launches.load(); }
 
 extern "C" const char* b200dp_error_string(int code) {
   switch (code) {
@@ -185,6 +192,15 @@ extern "C" int b200dp_comm_all_gather32(b200dp_comm* comm, const void* in, int k
   gather32_kernel<<<blocks, 256, 0, s>>>(b200dp_make_peers(comm), seq, static_cast<const uint32_t*>(in), k,
                                          static_cast<uint32_t*>(out));
   B200DP_LAUNCH_CHECK();
+  return B200DP_OK;
+}
+
+// The error word copied to pinned host memory on `stream`, without blocking the host: the training loop
+// enqueues this every few steps and looks at what the previous copy brought back.
+extern "C" int b200dp_comm_error_async(b200dp_comm* comm, uint32_t* host_word, b200dp_stream_t stream) {
+  if (!comm || !host_word) return B200DP_EINVAL;
+  B200DP_CUDA_TRY(cudaMemcpyAsync(host_word, &comm->sync[comm->rank]->error, sizeof(uint32_t),
+                                  cudaMemcpyDeviceToHost, (cudaStream_t)stream));
   return B200DP_OK;
 }
 

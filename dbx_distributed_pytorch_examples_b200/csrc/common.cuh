@@ -3,6 +3,7 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "../../include/b200dp.h"
 
@@ -18,11 +19,16 @@
     if (_e != cudaSuccess) return (int)_e;    \
   } while (0)
 
-// A launch error must not stay sticky in the runtime's last-error slot.
+// Kernels this library has launched in this process (comm.cu owns the counter; b200dp_kernel_launches()).
+extern "C" unsigned long long b200dp_count_launch(void);
+
+// After every kernel launch: a launch error must not stay sticky in the runtime's last-error slot; a
+// successful launch is counted.
 #define B200DP_LAUNCH_CHECK()                 \
   do {                                        \
     cudaError_t _e = cudaGetLastError();      \
     if (_e != cudaSuccess) return (int)_e;    \
+    b200dp_count_launch();                    \
   } while (0)
 
 namespace b200dp {
@@ -84,26 +90,51 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
 __device__ __forceinline__ void st_ll(uint2* p, float v, uint32_t seq) {
   asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(__float_as_uint(v)), "r"(seq) : "memory");
 }
-// Poll an LL word until it carries `seq`; false on timeout (~10 s).
-__device__ __forceinline__ bool ld_ll(const uint2* p, uint32_t seq, float* out) {
+// Two adjacent LL words with one 16-byte store (p 16-byte aligned).  Each 8-byte half is a complete
+// {value, seq} word of its own, so a reader that sees only one half updated simply keeps polling the other.
+__device__ __forceinline__ void st_ll2(uint2* p, float v0, float v1, uint32_t seq) {
+  const unsigned long long hi = (unsigned long long)seq << 32;
+  asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(hi | __float_as_uint(v0)),
+               "l"(hi | __float_as_uint(v1))
+               : "memory");
+}
+// Default bound of every wait on a peer, in SM cycles: about 10 minutes at 2 GHz, the order of NCCL's
+// watchdog.  B200DP_TIMEOUT_S overrides it (read once by b200dp_make_peers).
+#define B200DP_DEFAULT_TIMEOUT_CYCLES (600LL * 2000000000LL)
+// Poll an LL word until it carries `seq`; false once `timeout` cycles have passed.
+__device__ __forceinline__ bool ld_ll(const uint2* p, uint32_t seq, float* out, long long timeout) {
   uint32_t a, b;
   long long t0 = 0;
   while (true) {
     asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(a), "=r"(b) : "l"(p) : "memory");
     if (b == seq) break;
     if (t0 == 0) t0 = clock64();
-    if (clock64() - t0 > (20LL << 30)) { *out = 0.f; return false; }
+    if (clock64() - t0 > timeout) { *out = 0.f; return false; }
   }
   *out = __uint_as_float(a);
   return true;
 }
+// Same for two adjacent words read with one 16-byte load.
+__device__ __forceinline__ bool ld_ll2(const uint2* p, uint32_t seq, float* out0, float* out1, long long timeout) {
+  unsigned long long a, b;
+  long long t0 = 0;
+  while (true) {
+    asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
+    if ((uint32_t)(a >> 32) == seq && (uint32_t)(b >> 32) == seq) break;
+    if (t0 == 0) t0 = clock64();
+    if (clock64() - t0 > timeout) { *out0 = *out1 = 0.f; return false; }
+  }
+  *out0 = __uint_as_float((uint32_t)a);
+  *out1 = __uint_as_float((uint32_t)b);
+  return true;
+}
 // Spin until *p has reached `seq` (wrap-safe).  Returns false on timeout so a
 // dead peer turns into an error flag instead of a hung GPU.
-__device__ __forceinline__ bool wait_flag(const uint32_t* p, uint32_t seq) {
+__device__ __forceinline__ bool wait_flag(const uint32_t* p, uint32_t seq, long long timeout) {
   long long t0 = clock64();
   while ((int32_t)(ld_acquire_sys(p) - seq) < 0) {
     __nanosleep(20);
-    if (clock64() - t0 > (20LL << 30)) return false;  // ~10 s at 2 GHz
+    if (clock64() - t0 > timeout) return false;
   }
   return true;
 }
@@ -226,17 +257,30 @@ struct b200dp_comm {
   uint32_t seq;
 };
 
-// Passed by value to kernels.
+// Passed by value to kernels (as a __grid_constant__ parameter wherever sync[] is indexed at run time,
+// so that the index goes to the constant bank instead of a local-memory copy of the struct).
 struct b200dp_peers {
   int rank;
   int world;
+  long long timeout;  // cycles a kernel waits for a peer before it raises the error word and gives up
   b200dp_sync_area* sync[B200DP_MAX_WORLD];
 };
+
+// Wait bound in cycles: B200DP_TIMEOUT_S seconds (default 600) at a nominal 2 GHz, read once.
+static inline long long b200dp_timeout_cycles() {
+  static const long long cycles = [] {
+    const char* e = getenv("B200DP_TIMEOUT_S");
+    const double s = e && e[0] ? atof(e) : 0.0;
+    return s > 0.0 ? (long long)(s * 2.0e9) : B200DP_DEFAULT_TIMEOUT_CYCLES;
+  }();
+  return cycles;
+}
 
 static inline b200dp_peers b200dp_make_peers(const b200dp_comm* c) {
   b200dp_peers p;
   p.rank = c ? c->rank : 0;
   p.world = c ? c->world : 1;
+  p.timeout = b200dp_timeout_cycles();
   for (int i = 0; i < B200DP_MAX_WORLD; ++i) p.sync[i] = c ? c->sync[i] : nullptr;
   return p;
 }

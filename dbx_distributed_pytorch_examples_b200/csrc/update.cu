@@ -3,7 +3,7 @@
 //
 // Two-shot (large buckets):  rank r owns the r-th 1/world slice of the bucket.
 //   wait until every rank has raised `ready`            (grads are packed)
-//   for each 8-element unit of my slice:
+//   for each 16-byte vector of my slice (one per thread and pass):
 //       g  = sum over ranks, in rank order, of that unit read from the rank's
 //            bucket (ld.global.cg on the IPC-mapped pointer: an NVLink load)
 //       SGD-momentum / Adam on my master weights and state (local HBM, fp32)
@@ -71,37 +71,30 @@ struct FusedArgs {
   uint32_t seq;
 };
 
-template <typename T>
-__device__ __forceinline__ void load8(const T* p, float* f);
-template <>
-__device__ __forceinline__ void load8<float>(const float* p, float* f) {
-  Vec<float>::unpack(ld_cg(p), f);
-  Vec<float>::unpack(ld_cg(p + 4), f + 4);
+// A thread's unit of work is ONE 16-byte vector of the bucket (E = 4 fp32 or 8 bf16 elements), so that a
+// warp's request to a rank is 512 contiguous bytes whatever the element type.  (Two adjacent 16-byte
+// loads per thread, as an 8-element fp32 unit would need, make every warp request touch each 32-byte
+// sector twice; peer memory is not cached in the local L2, so that doubled the NVLink traffic of fp32
+// buckets.)  fp32 state for E elements is E/4 vectors.
+template <int E>
+__device__ __forceinline__ void load_f32(const float* p, float* f) {
+#pragma unroll
+  for (int k = 0; k < E; k += 4) Vec<float>::unpack(ld_cg(p + k), f + k);
 }
-template <>
-__device__ __forceinline__ void load8<__nv_bfloat16>(const __nv_bfloat16* p, float* f) {
-  Vec<__nv_bfloat16>::unpack(ld_cg(p), f);
-}
-template <typename T>
-__device__ __forceinline__ void store8(T* p, const float* f);
-template <>
-__device__ __forceinline__ void store8<float>(float* p, const float* f) {
-  *reinterpret_cast<uint4*>(p) = Vec<float>::pack(f);
-  *reinterpret_cast<uint4*>(p + 4) = Vec<float>::pack(f + 4);
-}
-template <>
-__device__ __forceinline__ void store8<__nv_bfloat16>(__nv_bfloat16* p, const float* f) {
-  *reinterpret_cast<uint4*>(p) = Vec<__nv_bfloat16>::pack(f);
+template <int E>
+__device__ __forceinline__ void store_f32(float* p, const float* f) {
+#pragma unroll
+  for (int k = 0; k < E; k += 4) *reinterpret_cast<uint4*>(p + k) = Vec<float>::pack(f + k);
 }
 
-// One optimizer step on 8 elements.  g: averaged gradient (in), p/s1/s2 in-out.
+// One optimizer step on E elements.  g: averaged gradient (in), p/s1/s2 in-out.
 // Operation order follows torch's foreach kernels so that fp32 results agree to
 // the last bit or two (TORCH/optim/sgd.py:322-380, TORCH/optim/adam.py:347+).
-template <int OPT>
+template <int OPT, int E>
 __device__ __forceinline__ void opt_step(const b200dp_opt_args& o, float* g, float* p, float* s1,
                                          float* s2) {
 #pragma unroll
-  for (int k = 0; k < 8; ++k) {
+  for (int k = 0; k < E; ++k) {
     float gk = g[k];
     if (o.weight_decay != 0.f) gk = fmaf(p[k], o.weight_decay, gk);
     if (OPT == B200DP_OPT_SGD) {
@@ -130,64 +123,80 @@ __device__ __forceinline__ void opt_step(const b200dp_opt_args& o, float* g, flo
 }
 
 template <typename GT, typename PT, int OPT, int WORLD>
-__global__ void __launch_bounds__(kT, 1) fused_kernel(const FusedArgs A, b200dp_peers P) {
+__global__ void __launch_bounds__(kT, 1) fused_kernel(const __grid_constant__ FusedArgs A,
+                                                      const __grid_constant__ b200dp_peers P) {
   __shared__ bool is_last;
+  __shared__ int s_ok;
+  constexpr int E = Vec<GT>::N;  // elements per 16-byte vector
   const int tid = threadIdx.x;
   const int slot = A.seq % B200DP_BUCKET_FLAG_SLOTS;
   b200dp_sync_area* me = P.sync[P.rank];
   constexpr int world = WORLD;
 
   if (world > 1) {
+    if (tid == 0) s_ok = 1;
+    __syncthreads();
     if (blockIdx.x == 0 && tid < world) st_release_sys(&P.sync[tid]->ready[slot][P.rank], A.seq);
     if (tid < world) {
-      if (!wait_flag(&me->ready[slot][tid], A.seq)) atomicExch(&me->error, 1u);
+      if (!wait_flag(&me->ready[slot][tid], A.seq, P.timeout)) {
+        atomicExch(&me->error, 1u);
+        s_ok = 0;
+      }
     }
     __syncthreads();
+    // A peer never showed up: its bucket is stale.  Leave gradients, state and parameters alone
+    // (the host sees the error word and stops) rather than push a wrong update to everybody.
+    if (!s_ok) return;
   }
 
   const bool push = (world > 1) && !A.one_shot;
   PT* my_param = static_cast<PT*>(A.param[P.rank]);
-  const long long gsz = (long long)gridDim.x * kT * 8;
-  for (long long i = A.begin + ((long long)blockIdx.x * kT + tid) * 8; i < A.end; i += gsz) {
+  const long long gsz = (long long)gridDim.x * kT * E;
+  for (long long i = A.begin + ((long long)blockIdx.x * kT + tid) * E; i < A.end; i += gsz) {
     // all ranks' loads are issued before the first add (WORLD is a constant,
     // so this unrolls into WORLD independent NVLink requests per thread)
-    float g[8], h[WORLD > 1 ? WORLD - 1 : 1][8];
-    load8<GT>(static_cast<const GT*>(A.grad[0]) + i, g);
+    uint4 raw[WORLD];
 #pragma unroll
-    for (int r = 1; r < world; ++r) load8<GT>(static_cast<const GT*>(A.grad[r]) + i, h[r - 1]);
+    for (int r = 0; r < world; ++r) raw[r] = ld_cg(static_cast<const GT*>(A.grad[r]) + i);
+    float g[E];
+    Vec<GT>::unpack(raw[0], g);
 #pragma unroll
-    for (int r = 1; r < world; ++r) {
+    for (int r = 1; r < world; ++r) {  // rank order: every rank computes the same sum
+      float h[E];
+      Vec<GT>::unpack(raw[r], h);
 #pragma unroll
-      for (int k = 0; k < 8; ++k) g[k] += h[r - 1][k];
+      for (int k = 0; k < E; ++k) g[k] += h[k];
     }
     if (A.write_grads) {
+      const uint4 gv = Vec<GT>::pack(g);
       if (push) {
 #pragma unroll
         for (int r = 0; r < world; ++r)
-          store8<GT>(static_cast<GT*>(const_cast<void*>(A.grad[r])) + i, g);
+          *reinterpret_cast<uint4*>(static_cast<GT*>(const_cast<void*>(A.grad[r])) + i) = gv;
       } else {
-        store8<GT>(static_cast<GT*>(const_cast<void*>(A.grad[P.rank])) + i, g);
+        *reinterpret_cast<uint4*>(static_cast<GT*>(const_cast<void*>(A.grad[P.rank])) + i) = gv;
       }
     }
     if (OPT != B200DP_OPT_NONE) {
-      float p[8], s1[8], s2[8];
+      float p[E], s1[E], s2[E];
       if (A.master) {
-        load8<float>(A.master + i, p);
+        load_f32<E>(A.master + i, p);
       } else {
-        load8<PT>(my_param + i, p);
+        Vec<PT>::unpack(ld_cg(my_param + i), p);
       }
       if (OPT == B200DP_OPT_ADAM || (A.opt.momentum != 0.f && !A.opt.first_step))
-        load8<float>(A.s1 + i, s1);
-      if (OPT == B200DP_OPT_ADAM) load8<float>(A.s2 + i, s2);
-      opt_step<OPT>(A.opt, g, p, s1, s2);
-      if (A.master) store8<float>(A.master + i, p);
-      if (OPT == B200DP_OPT_ADAM || A.opt.momentum != 0.f) store8<float>(A.s1 + i, s1);
-      if (OPT == B200DP_OPT_ADAM) store8<float>(A.s2 + i, s2);
+        load_f32<E>(A.s1 + i, s1);
+      if (OPT == B200DP_OPT_ADAM) load_f32<E>(A.s2 + i, s2);
+      opt_step<OPT, E>(A.opt, g, p, s1, s2);
+      if (A.master) store_f32<E>(A.master + i, p);
+      if (OPT == B200DP_OPT_ADAM || A.opt.momentum != 0.f) store_f32<E>(A.s1 + i, s1);
+      if (OPT == B200DP_OPT_ADAM) store_f32<E>(A.s2 + i, s2);
+      const uint4 pv = Vec<PT>::pack(p);
       if (push) {
 #pragma unroll
-        for (int r = 0; r < world; ++r) store8<PT>(static_cast<PT*>(A.param[r]) + i, p);
+        for (int r = 0; r < world; ++r) *reinterpret_cast<uint4*>(static_cast<PT*>(A.param[r]) + i) = pv;
       } else {
-        store8<PT>(my_param + i, p);
+        *reinterpret_cast<uint4*>(my_param + i) = pv;
       }
     }
   }
@@ -205,7 +214,7 @@ __global__ void __launch_bounds__(kT, 1) fused_kernel(const FusedArgs A, b200dp_
     if (is_last && tid < world) {
       __threadfence_system();
       st_release_sys(&P.sync[tid]->done[slot][P.rank], A.seq);
-      if (!wait_flag(&me->done[slot][tid], A.seq)) atomicExch(&me->error, 1u);
+      if (!wait_flag(&me->done[slot][tid], A.seq, P.timeout)) atomicExch(&me->error, 1u);
     }
   }
 }
@@ -336,7 +345,7 @@ extern "C" int b200dp_allreduce_update(b200dp_comm* comm, size_t grad_heap_off, 
   A.write_grads = write_grads;
   A.seq = seq;
 
-  const long long units = (A.end - A.begin) / 8;
+  const long long units = (A.end - A.begin) / (grad_dtype == B200DP_BF16 ? 8 : 4);  // 16-byte vectors
   long long want = (units + kT - 1) / kT;
   int cap = max_ctas > 0 ? max_ctas : (world > 1 ? 64 : B200DP_NUM_SMS);
   if (cap > B200DP_NUM_SMS) cap = B200DP_NUM_SMS;  // every CTA must be resident: they elect a last one

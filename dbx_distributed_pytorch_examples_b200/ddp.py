@@ -176,6 +176,10 @@ class B200DDP(DistributedDataParallel):
         self._comm_hook = None
         self._iteration_armed = False
         self._bcast_buffers = None
+        self._iterations = 0
+        self._step_counted = False
+        self.error_poll_interval = 64
+        self._err_word = torch.zeros(1, dtype=torch.int32).pin_memory()
         self.bucket_bytes_cap = int((25 if bucket_cap_mb is None else bucket_cap_mb) * 1024 * 1024)
 
         if dist.is_available() and dist.is_initialized():
@@ -247,12 +251,20 @@ class B200DDP(DistributedDataParallel):
 
     # ---- forward ---------------------------------------------------------------------
     def forward(self, *inputs, **kwargs):
+        if getattr(self, "_unpickled", False):
+            if torch.is_grad_enabled() and any(p.requires_grad for p in self.module.parameters()) and self.training:
+                raise RuntimeError("this B200DDP was restored from a pickle and has no communicator: use it for "
+                                   "inference, or wrap .module in a new B200DDP to train")
+            return self.module(*inputs, **kwargs)
         if self.world > 1 and self.broadcast_buffers and self.require_forward_param_sync:
             # buffers of B200SyncBatchNorm layers are identical on all ranks by construction
             if self._bcast_buffers is None:  # computed once: the module tree does not change between steps
                 self._bcast_buffers = self._needs_buffer_broadcast()
-            for buf in self._bcast_buffers:
-                dist.broadcast(buf, src=0, group=self.process_group)
+            if self._bcast_buffers:
+                # one coalesced broadcast for all of them, like DDP's _sync_buffers
+                # (TORCH/nn/parallel/distributed.py:2214-2257 -> _distributed_broadcast_coalesced)
+                pg = self.process_group if self.process_group is not None else dist.group.WORLD
+                dist._broadcast_coalesced(pg, self._bcast_buffers, 250 * 1024 * 1024, 0)
         if torch.is_grad_enabled() and self.require_backward_grad_sync:
             self._arm_iteration()
         return self.module(*inputs, **kwargs)
@@ -267,9 +279,10 @@ class B200DDP(DistributedDataParallel):
         # one sequence number per bucket, reserved up front so that it does not
         # depend on the order in which gradients become ready
         self._seqs = [self.comm.next_seq() for _ in self._buckets]
-        if self._optimizer is not None:
-            self._opt_step_count += 1
-            self._state_stale = True
+        # the optimizer's step number advances when an update is actually issued (first bucket launch of
+        # this iteration), not here: a grad-enabled forward that is never followed by backward() must not
+        # shift Adam's bias correction or consume SGD's first step
+        self._step_counted = False
 
     @contextmanager
     def no_sync(self):
@@ -304,10 +317,31 @@ class B200DDP(DistributedDataParallel):
             self._next_bucket += 1
         torch.cuda.current_stream(self.device).wait_stream(self._comm_stream)
         self._iteration_armed = False
+        self._iterations += 1
+        if self.world > 1 and self._iterations % self.error_poll_interval == 0:
+            self._poll_error()
+
+    def _poll_error(self, blocking: bool = False):
+        """A kernel that gave up waiting for a peer raises the rank's error word and skips its update; the
+        replicas are then out of step and training must stop.  Every `error_poll_interval` iterations the
+        word is copied to pinned host memory behind the bucket kernels (no host synchronisation) and the
+        value the previous copy delivered is looked at; checkpoint paths read it synchronously."""
+        if blocking:
+            self.comm.check_error()
+            return
+        if int(self._err_word[0]) != 0:
+            raise _lib.B200DPError("a libb200dp kernel gave up waiting for a peer rank (peer dead or more than "
+                                   "B200DP_TIMEOUT_S seconds behind): the replicas are out of step, stop training")
+        _lib.check(_lib.lib().b200dp_comm_error_async(self.comm.handle, self._err_word.data_ptr(),
+                                                       self._comm_stream.cuda_stream), "b200dp_comm_error_async")
 
     def _launch_bucket(self, b: _BucketState):
         lib = _lib.lib()
         a = b.arena
+        if self._optimizer is not None and self._comm_hook is None and not self._step_counted:
+            self._opt_step_count += 1  # every bucket of this iteration uses the same step number
+            self._step_counted = True
+            self._state_stale = True
         cur = torch.cuda.current_stream(self.device)
         self._comm_stream.wait_stream(cur)
         with torch.cuda.stream(self._comm_stream):
@@ -408,22 +442,20 @@ class B200DDP(DistributedDataParallel):
                 raise NotImplementedError("parameter groups with different hyper-parameters are not fused")
         self._optimizer, self._opt_kind, self._opt_group = optimizer, kind, groups[0]
         self.materialize_grads = bool(materialize_grads)
-        self._opt_step_count = 0
         for a in self._arenas:
             a.state1 = torch.zeros(a.total, dtype=torch.float32, device=self.device)
             a.state2 = torch.zeros(a.total, dtype=torch.float32, device=self.device) if kind == _lib.OPT_ADAM else None
             a.master = a.flat_param.float() if a.dtype != torch.float32 else None
-            for p, off in zip(a.params, a.offsets):
-                st = optimizer.state[p]
-                if kind == _lib.OPT_SGD:
-                    st["momentum_buffer"] = a.state1[off:off + p.numel()].view(p.shape)
-                else:
-                    st["step"] = torch.tensor(0.0)
-                    st["exp_avg"] = a.state1[off:off + p.numel()].view(p.shape)
-                    st["exp_avg_sq"] = a.state2[off:off + p.numel()].view(p.shape)
-        ddp = self
+        # an optimizer that has already taken steps (or was restored from a checkpoint) keeps its state
+        self._adopt_optimizer_state()
         self._state_stale = False
         optimizer.register_state_dict_pre_hook(self._check_state_consolidated)
+        # optimizer.load_state_dict() replaces optimizer.state with fresh tensors: copy them into the arenas
+        # the kernels use and restore the step number (resume path of 01_basic_torch_distributor.py:109-119)
+        optimizer.register_load_state_dict_post_hook(lambda opt: self._adopt_optimizer_state())
+        # module.load_state_dict() writes the (bf16) parameters in place: the fp32 master copy follows
+        self._module_hook = self.module.register_load_state_dict_post_hook(lambda mod, keys: self._refresh_master())
+        ddp = self
 
         def step(opt_self, closure=None):
             loss = closure() if closure is not None else None
@@ -438,6 +470,47 @@ class B200DDP(DistributedDataParallel):
         import types
         optimizer.step = types.MethodType(step, optimizer)
         return optimizer
+
+    @torch.no_grad()
+    def _adopt_optimizer_state(self):
+        """Copy whatever per-parameter state the optimizer holds (momentum_buffer / exp_avg / exp_avg_sq /
+        step — from earlier un-fused steps or from ``optimizer.load_state_dict``) into the flat arenas the
+        kernels update, re-point the optimizer's entries at views of those arenas, and restore the step
+        number (Adam's bias correction, SGD's "first step" rule)."""
+        opt, kind = self._optimizer, self._opt_kind
+
+        def adopt(st, key, arena_slice, p):
+            old = st.get(key)
+            if old is None:
+                arena_slice.zero_()
+            elif old.data_ptr() != arena_slice.data_ptr():
+                arena_slice.copy_(_flat_like(old, p))
+            st[key] = _strided_like(arena_slice, p)
+            return old is not None
+
+        count = 0
+        for a in self._arenas:
+            for p, off in zip(a.params, a.offsets):
+                st = opt.state[p]
+                v1 = a.state1[off:off + p.numel()]
+                if kind == _lib.OPT_SGD:
+                    if adopt(st, "momentum_buffer", v1, p):
+                        count = max(count, 1, self._opt_step_count)  # a buffer exists: the first step is behind us
+                else:
+                    adopt(st, "exp_avg", v1, p)
+                    adopt(st, "exp_avg_sq", a.state2[off:off + p.numel()], p)
+                    t = st.get("step")
+                    t = float(t) if t is not None else 0.0
+                    st["step"] = torch.tensor(t)
+                    count = max(count, int(t))
+        self._opt_step_count = count
+        self._state_stale = False  # written whole: every rank holds all of it until the next sharded update
+
+    @torch.no_grad()
+    def _refresh_master(self):
+        for a in self._arenas:
+            if a.master is not None:
+                a.master.copy_(a.flat_param)
 
     def _opt_args(self, arena) -> _lib.OptArgs:
         o = _lib.OptArgs()
@@ -476,6 +549,7 @@ class B200DDP(DistributedDataParallel):
             self._state_stale = False
             return
         torch.cuda.current_stream(self.device).wait_stream(self._comm_stream)
+        self._poll_error(blocking=True)  # never write a checkpoint from replicas that fell out of step
         for b in self._buckets:
             a = b.arena
             sl = b.numel // self.world
@@ -498,7 +572,45 @@ class B200DDP(DistributedDataParallel):
         return [b.numel * b.arena.esize for b in self._buckets]
 
     def __getstate__(self):
-        raise NotImplementedError("pickle module.state_dict() (or .module) instead of the B200DDP wrapper")
+        """Pickle support for ``mlflow.pytorch.log_model(ddp_model, ...)``
+        (01_torch_distributor/01_basic_torch_distributor.py:303), which pickles the wrapper itself.  What is
+        saved is the wrapped module with its parameters copied OUT of the peer-visible heap (a parameter here is
+        a view of one large allocation, which must not travel) plus the constructor's settings; the
+        communicator, streams and hooks are not."""
+        import copy
+
+        memo = {id(p): torch.nn.Parameter(p.detach().clone(memory_format=torch.preserve_format), requires_grad=p.requires_grad)
+                for p in self.module.parameters()}
+        from .fusion import unfuse_bn_relu
+
+        module = copy.deepcopy(self.module, memo)
+        hook = getattr(self, "_module_hook", None)
+        if hook is not None:  # the master-weight refresh hook closes over this wrapper
+            module._load_state_dict_post_hooks.pop(hook.id, None)
+        unfuse_bn_relu(module)  # fused blocks carry an instance-bound forward that cannot be unpickled
+        return {"module": module, "device_ids": self.device_ids,
+                "output_device": self.output_device, "broadcast_buffers": self.broadcast_buffers,
+                "bucket_cap_mb": self.bucket_bytes_cap / (1024 * 1024), "one_shot_bytes": self.one_shot_bytes,
+                "max_ctas": self.max_ctas}
+
+    def __setstate__(self, state):
+        """An unpickled wrapper carries the module for inference / export (``.module``, ``state_dict()``,
+        ``forward`` under ``torch.no_grad()``); to train again wrap ``.module`` in a new ``B200DDP`` inside an
+        initialised process group (the peer mappings cannot be restored from a file)."""
+        torch.nn.Module.__init__(self)
+        self.module = state["module"]
+        self.device_ids, self.output_device = state["device_ids"], state["output_device"]
+        self.broadcast_buffers = state["broadcast_buffers"]
+        self.bucket_bytes_cap = int(state["bucket_cap_mb"] * 1024 * 1024)
+        self.one_shot_bytes, self.max_ctas = state["one_shot_bytes"], state["max_ctas"]
+        self.world, self.rank = 1, 0
+        self.process_group = None
+        self.require_backward_grad_sync = self.require_forward_param_sync = True
+        self._optimizer = self._comm_hook = None
+        self._unpickled = True
+
+    def _get_name(self):
+        return "B200DDP"
 
     def _get_ddp_logging_data(self):
         return {"backend_name": "b200dp-nvlink-p2p", "world_size": self.world, "rank": self.rank}
@@ -529,6 +641,14 @@ def prepare_model(model: torch.nn.Module, device=None, *, sync_batchnorm: bool =
     if channels_last:
         model = model.to(memory_format=torch.channels_last)
     return B200DDP(model, device_ids=[device.index], output_device=device.index, **ddp_kwargs)
+
+
+def _flat_like(t: torch.Tensor, p: torch.Tensor) -> torch.Tensor:
+    """`t` (a state tensor shaped like p) as a 1-D fp32 tensor in p's physical element order."""
+    t = t.to(device=p.device, dtype=torch.float32)
+    if not _same_layout(t, p):
+        t = torch.empty_like(p, dtype=torch.float32).copy_(t)
+    return t.as_strided((p.numel(),), (1,), t.storage_offset()) if p.numel() else t.reshape(-1)
 
 
 def _same_layout(g: torch.Tensor, p: torch.Tensor) -> bool:

@@ -94,3 +94,24 @@ def fuse_bn_relu(model: nn.Module) -> nn.Module:
             if pool.supported(m.maxpool):
                 m.maxpool = pool.B200MaxPool2d.from_module(m.maxpool)
     return model
+
+
+def unfuse_bn_relu(model: nn.Module) -> nn.Module:
+    """Undo :func:`fuse_bn_relu` in place: the blocks get their class ``forward`` back, the BN layers stop
+    applying ReLU / taking the skip tensor, the stem gets its ``nn.ReLU`` and ``nn.MaxPool2d`` again.
+    ``B200DDP.__getstate__`` pickles such a copy: a module whose ``forward`` is an instance attribute bound
+    to a function of this file cannot be unpickled, a plain torchvision / reference block can."""
+    for m in model.modules():
+        if "forward" in m.__dict__ and getattr(m.__dict__["forward"], "__func__", None) in (_basic_forward, _bottleneck_forward):
+            del m.__dict__["forward"]
+            for name in ("bn1", "bn2", "bn3"):
+                bn = getattr(m, name, None)
+                if _is_ours(bn):
+                    bn.fuse_relu = False
+        elif _looks_like_resnet_stem(m) and isinstance(m.relu, nn.Identity) and m.bn1.fuse_relu:
+            m.bn1.fuse_relu = False
+            m.relu = nn.ReLU(inplace=True)
+            if isinstance(m.maxpool, pool.B200MaxPool2d):
+                p = m.maxpool
+                m.maxpool = nn.MaxPool2d(p.kernel_size, p.stride, p.padding, p.dilation, p.return_indices, p.ceil_mode)
+    return model

@@ -84,9 +84,14 @@ class B200MaxPool2d(nn.MaxPool2d):
 
     def forward(self, input: torch.Tensor) -> torch.Tensor:
         C = input.shape[1] if input.dim() == 4 else 0
-        if input.dim() != 4 or C % (8 if input.dtype == torch.bfloat16 else 4) or input.dtype not in (torch.float32, torch.bfloat16):
-            # shapes the kernel does not take (3D input, odd channel counts, other dtypes) stay on torch's own op
-            return super().forward(input)
+        if not input.is_cuda:
+            raise ValueError("B200MaxPool2d expected a CUDA tensor; there is no CPU path here")
+        if (input.dim() != 4 or input.dtype not in (torch.float32, torch.bfloat16)
+                or C % (8 if input.dtype == torch.bfloat16 else 4)):
+            # no second implementation behind this module: say so instead of quietly running another kernel
+            raise ValueError("B200MaxPool2d takes 4-D tensors of float32 (C % 4 == 0) or bfloat16 (C % 8 == 0); "
+                             f"got {tuple(input.shape)} {input.dtype} on {input.device}. Keep nn.MaxPool2d for this layer "
+                             "(fuse_bn_relu only swaps the ResNet stem's pooling layer).")
         return _MaxPool.apply(input, self._k, self._s, self._p)
 
     @classmethod

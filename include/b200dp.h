@@ -52,6 +52,9 @@ typedef void* b200dp_stream_t;
 typedef struct b200dp_comm b200dp_comm; /* opaque: IPC-mapped peer buffers + flags */
 
 int b200dp_version(void);
+/* Number of CUDA kernels this library has launched in this process so far (all entry points, all
+ * threads).  bench.py reports the difference over its timed region as `gpu_launches`. */
+unsigned long long b200dp_kernel_launches(void);
 /* Static string for a code returned by any entry point (never NULL). */
 const char* b200dp_error_string(int code);
 
@@ -265,6 +268,20 @@ int b200dp_bn_backward(const void* dy, const void* x, const void* y_out, void* d
                        float* grad_weight, float* grad_bias, b200dp_comm* comm,
                        uint32_t seq, b200dp_stream_t stream);
 
+/* 1 when b200dp_bn_forward (backward != 0: b200dp_bn_backward) runs a layer of this shape as ONE
+ * kernel, 0 when it issues two.  Layers whose tensor fits the L2 (B200DP_BN_FUSED_MB /
+ * B200DP_BN_FUSED_BWD_MB MiB, environment; B200DP_BN_FUSED=0 turns the path off) are handled by one
+ * thread-block cluster per channel chunk: rows streamed once for the statistics (sums), folded over the
+ * cluster through distributed shared memory, exchanged across ranks, and streamed again out of the L2
+ * for the normalise (dx) pass.  Same arguments, same results, same exchange words as the two-kernel
+ * path (ranks with different local batch sizes may take different paths in the same step).
+ * For callers that time or count launches. */
+int b200dp_bn_one_kernel(int dtype, int64_t M, int C, int backward);
+/* The same limits at run time (tests, A/B measurements): MiB bounds for the forward / backward
+ * (0 = never take the one-kernel path, < 0 = leave unchanged) and the cluster size (8 or 16; anything
+ * else = leave unchanged).  Not synchronised with calls in flight on other host threads. */
+int b200dp_bn_set_one_kernel_limits(int fwd_mb, int bwd_mb, int cluster_size);
+
 /* ------------------------------------------------------------------------
  * Communicator: library-owned symmetric buffers mapped into every rank.
  *
@@ -297,8 +314,6 @@ size_t b200dp_comm_heap_bytes(const b200dp_comm* comm);
  * below and every SyncBN exchange consumes one, in the same order on every
  * rank. */
 uint32_t b200dp_comm_next_seq(b200dp_comm* comm);
-/* Device-side barrier across the ranks on `stream` (a kernel that signals
- * every peer and waits for every peer); used at set-up and in tests. */
 /* All-gather of k 32-bit words (float32 or int32, bit-exact) per rank: out[r*k + j] = rank r's in[j].
  * One small kernel over the peer-mapped exchange slots; stands for the per-epoch metric gathers of the
  * reference (04_accelerate/01_cifar_accelerate.ipynb:638-640: three accelerator.gather calls on
@@ -306,11 +321,22 @@ uint32_t b200dp_comm_next_seq(b200dp_comm* comm);
  * relative to its other collective calls.  k <= 2*B200DP_BN_MAX_CHANNELS + 128. */
 int b200dp_comm_all_gather32(b200dp_comm* comm, const void* in, int k, void* out,
                              b200dp_stream_t stream);
+/* Device-side barrier across the ranks on `stream` (a kernel that signals
+ * every peer and waits for every peer); used at set-up and in tests. */
 int b200dp_comm_barrier(b200dp_comm* comm, b200dp_stream_t stream);
 /* Synchronous read of the rank's error word: non-zero once a kernel on this
- * rank gave up waiting (about 10 s) for a peer's flag.  Takes the place of the
- * NCCL watchdog / TORCH_DISTRIBUTED_DEBUG checks (setup/00_setup.py:66-67). */
+ * rank gave up waiting for a peer (flag or exchange word).  The bound of every
+ * such wait is B200DP_TIMEOUT_S seconds (environment, default 600: the order of
+ * the NCCL watchdog's 10 minutes); a kernel whose wait ran out raises the word,
+ * skips its update / push and returns, so the replicas are no longer in step
+ * and the host must stop.  Takes the place of the NCCL watchdog /
+ * TORCH_DISTRIBUTED_DEBUG checks (setup/00_setup.py:66-67). */
 int b200dp_comm_error(b200dp_comm* comm);
+/* The same word copied into `host_word` (PINNED host memory, 4 bytes) on
+ * `stream` without blocking the host: enqueue it every few steps and look at
+ * the value the previous copy delivered. */
+int b200dp_comm_error_async(b200dp_comm* comm, uint32_t* host_word,
+                            b200dp_stream_t stream);
 
 /* ------------------------------------------------------------------------
  * (1) Gradient bucket: pack -> all-reduce fused with 1/N and the optimizer.

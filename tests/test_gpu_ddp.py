@@ -122,18 +122,47 @@ def test_bf16_model_with_syncbn_fusion_trains():
     torch.testing.assert_close(m.bn1.running_mean, ref.bn1.running_mean, rtol=5e-2, atol=2e-2)
 
 
-def test_per_tensor_grads_with_channels_last_input():
-    """Every parameter's gradient, SyncBN-converted + fused + wrapped, against plain torch on the same
-    weights and batch.  (1x1 conv weight gradients arrive with channels_last strides: the pack must
-    treat them as the same memory and must keep converted copies alive until it has run.)"""
+def _grad_errors_against_float64(x, y, build_ours):
+    """Weight gradients of the reference ResNet-18 on one batch, three ways: torch in float64 (the arbiter),
+    torch in float32, and `build_ours(model)` in float32.  Returns {name: (err_ours, err_torch32)}, each a
+    relative L2 distance to the float64 gradient of that tensor."""
     ref, m = make_pair()
-    ddp = b200.B200DDP(b200.fuse_bn_relu(b200.convert_sync_batchnorm(m)), device_ids=[0])
-    x, y = batch(0, 64)
+    arb = copy.deepcopy(ref).double()
+    F.cross_entropy(arb(x.double()), y).backward()
     F.cross_entropy(ref(x), y).backward()
-    F.cross_entropy(ddp(x.contiguous(memory_format=torch.channels_last)), y).backward()
-    for (n, a), b in zip(ref.named_parameters(), m.parameters()):
-        err = float((b.grad - a.grad).norm() / (a.grad.norm() + 1e-20))
-        assert err < 2e-2, (n, err)
+    ours = build_ours(m)
+    F.cross_entropy(ours(x.contiguous(memory_format=torch.channels_last)), y).backward()
+    out = {}
+    for (n, a), t, o in zip(arb.named_parameters(), ref.parameters(), m.parameters()):
+        g = a.grad
+        out[n] = (float((o.grad.double() - g).norm() / g.norm()), float((t.grad.double() - g).norm() / g.norm()))
+    return out
+
+
+def test_per_tensor_grads_against_float64_arbiter():
+    """Every parameter's gradient with the SyncBN-converted, fused, wrapped model against plain torch — with
+    a float64 run of the same model as the arbiter.  Two float32 runs of a 20-BatchNorm network differ from
+    EACH OTHER by up to ~1e-2 at the stem (round-off amplified through the BN backward passes); what can be
+    asked of an implementation is that it is as close to the float64 truth as torch's own float32 kernels
+    are, tensor by tensor.  (1x1 conv weight gradients arrive with channels_last strides: the pack must
+    treat them as the same memory and must keep converted copies alive until it has run.)"""
+    x, y = batch(0, 64)
+    errs = _grad_errors_against_float64(
+        x, y, lambda m: b200.B200DDP(b200.fuse_bn_relu(b200.convert_sync_batchnorm(m)), device_ids=[0]))
+    worst_ratio = max(eo / max(et, 1e-7) for eo, et in errs.values())
+    for n, (eo, et) in errs.items():
+        assert eo <= 2.0 * et + 1e-6, (n, eo, et)
+    # and summed over the network neither implementation is systematically closer
+    tot_o = sum(eo for eo, _ in errs.values()); tot_t = sum(et for _, et in errs.values())
+    assert tot_o <= 1.5 * tot_t, (tot_o, tot_t, worst_ratio)
+
+
+def test_plain_bn_model_grads_against_float64_arbiter():
+    """The same measurement without our BatchNorm (wrapper only): the pack + reduce path adds nothing."""
+    x, y = batch(1, 64)
+    errs = _grad_errors_against_float64(x, y, lambda m: b200.B200DDP(m, device_ids=[0]))
+    for n, (eo, et) in errs.items():
+        assert eo <= 1.2 * et + 1e-7, (n, eo, et)
 
 
 def test_comm_hook_compat():
@@ -228,11 +257,172 @@ def test_200_step_loss_curve_full_stack_fp32():
         o_ref.zero_grad(); o_our.zero_grad()
         l_ref = F.cross_entropy(ref(x), y); l_ref.backward(); o_ref.step()
         l_our = F.cross_entropy(ddp(x.contiguous(memory_format=torch.channels_last)), y); l_our.backward(); o_our.step()
-        if step % 10 == 9 or step < 3:
-            worst = max(worst, abs(float(l_our) - float(l_ref)) / float(l_ref))
+        worst = max(worst, abs(float(l_our) - float(l_ref)) / float(l_ref))   # every step
     assert worst < 0.01, worst
     assert int(m.bn1.num_batches_tracked) == int(ref.bn1.num_batches_tracked) == 200
     torch.testing.assert_close(m.bn1.running_var, ref.bn1.running_var, rtol=1e-3, atol=1e-5)
+
+
+def test_200_step_loss_curve_full_stack_bf16():
+    """The same 200 steps in the headline dtype: bf16 channels_last model, fused SyncBN(+add)+ReLU, stem pooling,
+    fused SGD on fp32 master weights — against stock torch running the SAME recipe in bf16 (nn.BatchNorm2d,
+    torch.optim.SGD on bf16 weights would stall at lr 1e-3, so the torch side keeps fp32 weights under
+    autocast-free explicit casts: fp32 master copy + bf16 compute copy, which is what our master weights are).
+    Every step's loss within 1 % (north_star)."""
+    ref, m = make_pair()
+    ref_bf = copy.deepcopy(ref).to(torch.bfloat16).to(memory_format=torch.channels_last)
+    for mod in ref_bf.modules():        # torch keeps BN parameters / statistics in fp32 under mixed precision
+        if isinstance(mod, torch.nn.BatchNorm2d):
+            mod.float()
+    m = b200.fuse_bn_relu(b200.convert_sync_batchnorm(m)).to(torch.bfloat16).to(memory_format=torch.channels_last)
+    ddp = b200.B200DDP(m, device_ids=[0])
+    o_our = ddp.fuse_optimizer(torch.optim.SGD(ddp.parameters(), lr=1e-3, momentum=0.5))
+    master = [p.detach().float().clone() for p in ref_bf.parameters()]     # fp32 master weights of the torch side
+    o_ref = torch.optim.SGD(master, lr=1e-3, momentum=0.5)
+    worst = 0.0
+    for step in range(200):
+        x, y = batch(step, 128)
+        xb = x.bfloat16().contiguous(memory_format=torch.channels_last)
+        for p in ref_bf.parameters():
+            p.grad = None
+        l_ref = F.cross_entropy(ref_bf(xb).float(), y); l_ref.backward()
+        for mp, p in zip(master, ref_bf.parameters()):
+            mp.grad = p.grad.float()
+        o_ref.step()
+        with torch.no_grad():
+            for mp, p in zip(master, ref_bf.parameters()):
+                p.copy_(mp)
+        o_our.zero_grad()
+        l_our = F.cross_entropy(ddp(xb).float(), y); l_our.backward(); o_our.step()
+        worst = max(worst, abs(float(l_our) - float(l_ref)) / float(l_ref))
+    assert worst < 0.01, worst
+
+
+def test_forward_without_backward_does_not_advance_the_optimizer():
+    """A training-mode forward that is never followed by backward() (a probe, or the reference's habit of
+    evaluating with the model left in train mode) must not move Adam's bias correction or use up SGD's first
+    step: the step number advances when an update is issued."""
+    for mk in (lambda p: torch.optim.Adam(p, lr=1e-3), lambda p: torch.optim.SGD(p, lr=1e-2, momentum=0.9)):
+        ref, m = make_pair()
+        ddp = b200.B200DDP(m, device_ids=[0])
+        o_ref, o_our = mk(ref.parameters()), mk(ddp.parameters())
+        ddp.fuse_optimizer(o_our)
+        ddp(batch(9)[0])                               # grad-enabled forward, no backward: before the first step
+        for step in range(3):
+            x, y = batch(step)
+            o_ref.zero_grad(); o_our.zero_grad()
+            F.cross_entropy(ref(x), y).backward(); o_ref.step()
+            F.cross_entropy(ddp(x), y).backward(); o_our.step()
+            ddp(batch(10 + step)[0]); ref(batch(10 + step)[0])   # probes in between (BN statistics move on both sides)
+        assert ddp._opt_step_count == 3
+        a, b = next(iter(ref.parameters())), next(iter(m.parameters()))
+        if isinstance(o_ref, torch.optim.SGD):
+            torch.testing.assert_close(b, a, rtol=1e-5, atol=1e-6)
+        else:
+            assert float((b - a).abs().mean()) < 1e-4
+
+
+def test_accelerate_recipe_adam_weight_decay_cosine():
+    """The Accelerate notebook's optimizer set-up on the fused path (04_accelerate/01_cifar_accelerate.ipynb:
+    482-487): Adam(lr, weight_decay=1e-4) + CosineAnnealingLR, stepped once per iteration here.  The learning
+    rate reaches the kernel every step; losses follow torch's within 1 %."""
+    ref, m = make_pair()
+    ddp = b200.B200DDP(m, device_ids=[0])
+    o_ref = torch.optim.Adam(ref.parameters(), lr=1e-3, weight_decay=1e-4)
+    o_our = ddp.fuse_optimizer(torch.optim.Adam(ddp.parameters(), lr=1e-3, weight_decay=1e-4))
+    s_ref = torch.optim.lr_scheduler.CosineAnnealingLR(o_ref, T_max=30)
+    s_our = torch.optim.lr_scheduler.CosineAnnealingLR(o_our, T_max=30)
+    for step in range(30):
+        x, y = batch(step, 64)
+        o_ref.zero_grad(); o_our.zero_grad()
+        l_ref = F.cross_entropy(ref(x), y); l_ref.backward(); o_ref.step(); s_ref.step()
+        l_our = F.cross_entropy(ddp(x), y); l_our.backward(); o_our.step(); s_our.step()
+        assert o_our.param_groups[0]["lr"] == o_ref.param_groups[0]["lr"]
+        assert abs(float(l_our) - float(l_ref)) < 0.01 * float(l_ref), (step, float(l_our), float(l_ref))
+    assert o_our.param_groups[0]["lr"] == pytest.approx(0.0, abs=1e-12)
+
+
+@pytest.mark.parametrize("opt", ["sgd", "adam"])
+def test_checkpoint_resume_through_the_fused_optimizer(opt):
+    """save_checkpoint / load_checkpoint of the reference (01_basic_torch_distributor.py:109-119,239-245):
+    train, save model + optimizer state, build everything anew, load, train on — equal to the uninterrupted
+    run.  Covers fuse_optimizer() adopting state the optimizer already holds, optimizer.load_state_dict() after
+    fusing, and the fp32 master weights following module.load_state_dict() for a bf16 model."""
+    import io
+    mk = (lambda p: torch.optim.SGD(p, lr=1e-2, momentum=0.9)) if opt == "sgd" else (lambda p: torch.optim.Adam(p, lr=1e-3))
+
+    def run(ddp, o, steps):
+        for step in steps:
+            x, y = batch(step)
+            o.zero_grad(); F.cross_entropy(ddp(x), y).backward(); o.step()
+
+    _, m_a = make_pair()
+    ddp_a = b200.B200DDP(m_a, device_ids=[0]); o_a = ddp_a.fuse_optimizer(mk(ddp_a.parameters()))
+    run(ddp_a, o_a, range(6))                                  # uninterrupted: 6 steps
+    _, m_b = make_pair()
+    ddp_b = b200.B200DDP(m_b, device_ids=[0]); o_b = ddp_b.fuse_optimizer(mk(ddp_b.parameters()))
+    run(ddp_b, o_b, range(3))
+    blob = io.BytesIO()
+    torch.save({"model": ddp_b.module.state_dict(), "optimizer": o_b.state_dict()}, blob)
+    blob.seek(0)
+    ck = torch.load(blob)
+    torch.manual_seed(123)                                     # a differently initialised model: everything comes from the file
+    m_c = workloads.cifar_resnet18(10).cuda()
+    ddp_c = b200.B200DDP(m_c, device_ids=[0]); o_c = ddp_c.fuse_optimizer(mk(ddp_c.parameters()))
+    ddp_c.module.load_state_dict(ck["model"]); o_c.load_state_dict(ck["optimizer"])
+    assert ddp_c._opt_step_count == 3
+    run(ddp_c, o_c, range(3, 6))
+    for (n, a), c in zip(m_a.named_parameters(), m_c.parameters()):
+        torch.testing.assert_close(c, a, rtol=1e-5, atol=1e-6, msg=lambda s: f"{n}: {s}")
+    # state an un-fused optimizer built up is adopted by fuse_optimizer()
+    _, m_d = make_pair()
+    ddp_d = b200.B200DDP(m_d, device_ids=[0]); o_d = mk(ddp_d.parameters())
+    run(ddp_d, o_d, range(3))                                  # plain mode: torch's own optimizer steps
+    ddp_d.fuse_optimizer(o_d)
+    assert ddp_d._opt_step_count == (3 if opt == "adam" else 1)
+    run(ddp_d, o_d, range(3, 6))
+    for (n, a), d in zip(m_a.named_parameters(), m_d.parameters()):
+        if opt == "sgd":
+            torch.testing.assert_close(d, a, rtol=1e-5, atol=1e-6, msg=lambda s: f"{n}: {s}")
+        else:
+            assert float((d - a).abs().mean()) < 1e-3, n
+
+
+def test_bf16_master_weights_follow_module_load_state_dict():
+    _, m = make_pair()
+    m = m.to(torch.bfloat16)
+    ddp = b200.B200DDP(m, device_ids=[0])
+    o = ddp.fuse_optimizer(torch.optim.SGD(ddp.parameters(), lr=0.0, momentum=0.0))
+    sd = {k: torch.zeros_like(v) for k, v in ddp.module.state_dict().items()}
+    ddp.module.load_state_dict(sd)
+    x, y = batch(0)
+    o.zero_grad(); F.cross_entropy(ddp(x.bfloat16()).float(), y).backward(); o.step()   # lr 0: parameters := master
+    torch.cuda.synchronize()
+    assert all(float(p.abs().max()) == 0.0 for p in m.parameters())   # the old master copy did not come back
+
+
+def test_pickle_round_trip_of_the_wrapper():
+    """mlflow.pytorch.log_model(ddp_model, ...) pickles the wrapper (01_basic_torch_distributor.py:303)."""
+    import pickle
+    _, m = make_pair()
+    m = b200.fuse_bn_relu(b200.convert_sync_batchnorm(m)).to(memory_format=torch.channels_last)
+    ddp = b200.B200DDP(m, device_ids=[0])
+    o = ddp.fuse_optimizer(torch.optim.SGD(ddp.parameters(), lr=1e-2, momentum=0.5))
+    x, y = batch(0)
+    o.zero_grad(); F.cross_entropy(ddp(x), y).backward(); o.step()
+    blob = pickle.dumps(ddp)
+    assert len(blob) < 60e6, "the pickle must not drag the peer-visible heap along"   # ResNet-18: 45 MB of weights
+    back = pickle.loads(blob)
+    assert isinstance(back, torch.nn.parallel.DistributedDataParallel) and isinstance(back, b200.B200DDP)
+    ddp.eval(); back.eval()
+    with torch.no_grad():
+        torch.testing.assert_close(back(x), ddp(x), rtol=1e-5, atol=1e-5)
+    assert list(back.module.state_dict()) == list(ddp.module.state_dict())
+    back.train()
+    with pytest.raises(RuntimeError, match="restored from a pickle"):
+        back(x)
+    # fuse -> unfuse is the identity on the module structure
+    assert not any("forward" in mod.__dict__ for mod in back.module.modules())
 
 
 def test_all_gather_scalars_single_process():

@@ -1,7 +1,8 @@
-"""GPU, 2 ranks (one process per GPU, NCCL only for set-up and as the comparison baseline):
-SyncBN statistics exchange, the fused all-reduce + optimizer kernel over peer memory, and the
-BASELINE config-1 training run (reference ResNet-18, batch 128/rank, SGD 1e-3/0.5, 200 steps)
-against the golden loss curve of stock DDP.  Run with `gpurun --gpus 2`."""
+"""GPU, 2 / 4 / 8 ranks (one process per GPU, NCCL only for set-up and as the comparison baseline):
+SyncBN statistics exchange, the fused all-reduce + optimizer kernel over peer memory, checkpoints of the
+sharded optimizer state, and the BASELINE config-1 training run (reference ResNet-18, batch 128/rank,
+SGD 1e-3/0.5, 200 steps) against the golden loss curve of stock DDP.  Every test runs at each world
+size the box has GPUs for: `gpurun --gpus 2` (or 4, 8) `-- python -m pytest tests/test_gpu_multi.py`."""
 import os
 
 import numpy as np
@@ -11,6 +12,14 @@ from dbx_distributed_pytorch_examples_b200 import TorchDistributor
 
 pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
 GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def _ngpu():
+    import torch
+    return torch.cuda.device_count() if torch.cuda.is_available() else 0
+
+
+WORLDS = [pytest.param(w, marks=pytest.mark.skipif(_ngpu() < w, reason=f"needs {w} GPUs")) for w in (2, 4, 8)]
 
 
 def _init():
@@ -29,6 +38,7 @@ def _w_syncbn():
     import torch
     import torch.distributed as dist
     import dbx_distributed_pytorch_examples_b200 as b200
+    from dbx_distributed_pytorch_examples_b200 import _lib
     rank, world = _init()
     g = np.load(os.path.join(GOLD, "syncbn.npz"))
     C, eps, mom = 16, float(g["eps"]), float(g["momentum"])
@@ -40,7 +50,7 @@ def _w_syncbn():
     def rows(t):
         return t.detach().float().permute(0, 2, 3, 1).reshape(-1, C).cpu().numpy()
 
-    for tag, relu, res in [("plain", False, False), ("relu", True, False), ("addrelu", True, True)]:
+    for tag, relu, res in [("plain", False, False), ("relu", True, False), ("addrelu", True, True)] if world == 2 else []:
         bn = b200.B200SyncBatchNorm(C, eps=eps, momentum=mom, fuse_relu=relu).cuda()
         with torch.no_grad():
             bn.weight.copy_(torch.from_numpy(g[f"{tag}_w"])); bn.bias.copy_(torch.from_numpy(g[f"{tag}_b"]))
@@ -60,27 +70,47 @@ def _w_syncbn():
         if res:
             np.testing.assert_allclose(rows(r.grad), g[f"{tag}_dr{rank}"], rtol=1e-6, atol=0)
 
-    # against torch's own SyncBatchNorm over NCCL, bf16 and fp32, uneven per-rank batch, many layers in a row
-    for dtype, tol in ((torch.float32, dict(rtol=1e-4, atol=1e-5)), (torch.bfloat16, dict(rtol=2e-2, atol=2e-2))):
-        torch.manual_seed(10 + rank)
-        for it, (n, c, hw) in enumerate([(8 + 4 * rank, 256, 14), (16, 64, 28), (4, 2048, 7), (6 - rank, 512, 7)] * 3):
-            ref = torch.nn.SyncBatchNorm(c).cuda()
-            ours = b200.B200SyncBatchNorm(c).cuda()
-            x = (torch.randn(n, c, hw, hw, device="cuda") * 2 + 1).to(dtype).contiguous(memory_format=torch.channels_last)
-            dy = torch.randn_like(x)
-            xa, xb = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
-            ya, yb = ours(xa), ref(xb)
-            ya.backward(dy); yb.backward(dy)
-            torch.testing.assert_close(ya, yb, **tol)
-            torch.testing.assert_close(xa.grad, xb.grad, rtol=tol["rtol"], atol=tol["atol"] * 4)
-            torch.testing.assert_close(ours.running_mean, ref.running_mean, rtol=1e-4, atol=1e-5)
-            torch.testing.assert_close(ours.running_var, ref.running_var, rtol=1e-3, atol=1e-5)
-            torch.testing.assert_close(ours.weight.grad, ref.weight.grad, rtol=2e-2, atol=2e-2 * hw)
+    # Against torch's own SyncBatchNorm over NCCL, bf16 and fp32, many layers in a row (more exchanges than
+    # slots), a different batch on every rank, the last rank EMPTY in some layers, and the three kernel-path
+    # settings: two kernels everywhere, one cluster kernel everywhere, and a size limit that puts the ranks
+    # with the larger batches on the two-kernel path and the others on the one-kernel path in the SAME exchange.
+    lib = _lib.lib()
+    worst = {}
+    for limits in ((0, 0, -1), (1 << 20, 1 << 20, 16), (1, 1, 8)):
+        lib.b200dp_bn_set_one_kernel_limits(*limits)
+        for dtype, tol in ((torch.float32, dict(rtol=1e-4, atol=1e-5)), (torch.bfloat16, dict(rtol=2e-2, atol=2e-2))):
+            torch.manual_seed(10 + rank)
+            shapes = [(8 + 4 * rank, 256, 14), (16, 64, 28), (4, 2048, 7), (6 + (rank % 3), 512, 7), (2 * rank, 128, 8)] * 2
+            for it, (n, c, hw) in enumerate(shapes):
+                if dtype == torch.bfloat16:
+                    n = max(n, 1)    # (torch's own SyncBatchNorm mixes dtypes in its all-gather when a bf16 rank is empty)
+                elif rank == world - 1 and it % 5 == 1:
+                    n = 0                                          # this rank has nothing in this layer
+                ref = torch.nn.SyncBatchNorm(c).cuda()
+                ours = b200.B200SyncBatchNorm(c).cuda()
+                x = (torch.randn(n, c, hw, hw, device="cuda") * 2 + 1).to(dtype).contiguous(memory_format=torch.channels_last)
+                dy = torch.randn_like(x)
+                xa, xb = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
+                ya, yb = ours(xa), ref(xb)
+                ya.backward(dy); yb.backward(dy)
+                torch.testing.assert_close(ya, yb, **tol)
+                torch.testing.assert_close(xa.grad, xb.grad, rtol=tol["rtol"], atol=tol["atol"] * 4)
+                torch.testing.assert_close(ours.running_mean, ref.running_mean, rtol=1e-4, atol=1e-5)
+                torch.testing.assert_close(ours.running_var, ref.running_var, rtol=1e-3, atol=1e-5)
+                torch.testing.assert_close(ours.weight.grad, ref.weight.grad, rtol=2e-2, atol=2e-2 * hw)
+                # every rank computed bit-identical statistics
+                stats = torch.cat([ours.running_mean, ours.running_var])
+                mine = stats.clone(); dist.broadcast(stats, src=0)
+                assert torch.equal(mine, stats), "ranks disagree on the merged statistics"
+                if n:
+                    key = ("y", str(dtype)); worst[key] = max(worst.get(key, 0.0), float((ya.float() - yb.float()).abs().max()))
+                    key = ("dx", str(dtype)); worst[key] = max(worst.get(key, 0.0), float((xa.grad.float() - xb.grad.float()).abs().max()))
+    lib.b200dp_bn_set_one_kernel_limits(56, 40, 16)
     from dbx_distributed_pytorch_examples_b200.comm import stats_communicator
     stats_communicator().check_error()
     dist.barrier()
     dist.destroy_process_group()
-    return "ok"
+    return {"%s_%s" % k: v for k, v in worst.items()}
 
 
 def _w_allreduce():
@@ -92,48 +122,63 @@ def _w_allreduce():
     from dbx_distributed_pytorch_examples_b200.comm import Communicator
     rank, world = _init()
     lib = _lib.lib()
+    q = 8 * world
+    worst = {}
     for dtype, tol in ((torch.float32, dict(rtol=1e-5, atol=1e-6)), (torch.bfloat16, dict(rtol=2e-2, atol=2e-2))):
         code, es = _lib.dtype_code(dtype), (2 if dtype == torch.bfloat16 else 4)
-        for n, one_shot in [(16, 0), (16, 1), (4096, 1), (1000 * 16, 0), (8 * 1024 * 1024, 0)]:
-            nbytes = (n * es + 511) // 512 * 512
-            comm = Communicator(heap_bytes=2 * nbytes)
-            grad, param = comm.heap_view(0, n, dtype), comm.heap_view(nbytes, n, dtype)
-            torch.manual_seed(7)
-            p0 = torch.randn(n, device="cuda")
-            param.copy_(p0)
-            master = p0.clone() if dtype == torch.bfloat16 else None
-            s1 = torch.zeros(n, device="cuda")
-            ref_p = torch.nn.Parameter(p0.clone())
-            ref_opt = torch.optim.SGD([ref_p], lr=0.1, momentum=0.9)
-            for step in range(3):
-                torch.manual_seed(100 * step + rank)
-                g = torch.randn(n, device="cuda").to(dtype)
-                grad.copy_((g.float() / world).to(dtype))          # what b200dp_bucket_pack leaves there
-                want = (g.float() / world).to(dtype).float()
-                dist.all_reduce(want)                               # NCCL baseline of the same sum
-                torch.cuda.synchronize(); dist.barrier()
-                o = _lib.OptArgs()
-                o.kind, o.lr, o.momentum, o.first_step = _lib.OPT_SGD, 0.1, 0.9, int(step == 0)
-                _lib.check(lib.b200dp_allreduce_update(
-                    comm.handle, 0, code, nbytes, code, 0, n, None if master is None else master.data_ptr(),
-                    s1.data_ptr(), None, ctypes.byref(o), one_shot, 0 if one_shot else 1, 0, comm.next_seq(),
-                    _lib.current_stream()))
-                torch.cuda.synchronize()
-                if not one_shot:                                    # averaged gradient written back everywhere
-                    torch.testing.assert_close(grad.float(), want.to(dtype).float(), **tol)
-                ref_p.grad = want.clone()
-                ref_opt.step()
-                torch.testing.assert_close(param.float(), ref_p.detach().to(dtype).float(), **tol)
-            # every rank holds the same parameters
-            mine = param.float().clone()
-            other = mine.clone()
-            dist.broadcast(other, src=0)
-            assert torch.equal(mine, other), "ranks disagree on the updated parameters"
-            comm.check_error()
-            dist.barrier()
-            comm.destroy()
+        for kind in ("sgd", "adam"):
+            for n, one_shot in [(q, 0), (q, 1), (256 * q, 1), (1000 * q, 0), (8 * 1024 * 1024, 0)]:
+                nbytes = (n * es + 511) // 512 * 512
+                comm = Communicator(heap_bytes=2 * nbytes)
+                grad, param = comm.heap_view(0, n, dtype), comm.heap_view(nbytes, n, dtype)
+                torch.manual_seed(7)
+                p0 = torch.randn(n, device="cuda")
+                param.copy_(p0)
+                master = p0.clone() if dtype == torch.bfloat16 else None
+                s1, s2 = torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda")
+                ref_p = torch.nn.Parameter(p0.clone() if master is not None else param.float().clone())
+                ref_opt = (torch.optim.SGD([ref_p], lr=0.1, momentum=0.9) if kind == "sgd"
+                           else torch.optim.Adam([ref_p], lr=1e-2, weight_decay=1e-4))
+                for step in range(3):
+                    torch.manual_seed(100 * step + rank)
+                    g = torch.randn(n, device="cuda").to(dtype)
+                    grad.copy_((g.float() / world).to(dtype))          # what b200dp_bucket_pack leaves there
+                    want = (g.float() / world).to(dtype).float()
+                    dist.all_reduce(want)                               # NCCL's sum of the same addends
+                    torch.cuda.synchronize(); dist.barrier()
+                    o = _lib.OptArgs()
+                    if kind == "sgd":
+                        o.kind, o.lr, o.momentum, o.first_step = _lib.OPT_SGD, 0.1, 0.9, int(step == 0)
+                    else:
+                        t = step + 1
+                        o.kind, o.lr, o.weight_decay, o.beta1, o.beta2, o.eps = _lib.OPT_ADAM, 1e-2, 1e-4, 0.9, 0.999, 1e-8
+                        o.step_size, o.bias_correction2_sqrt = 1e-2 / (1 - 0.9 ** t), math.sqrt(1 - 0.999 ** t)
+                    _lib.check(lib.b200dp_allreduce_update(
+                        comm.handle, 0, code, nbytes, code, 0, n, None if master is None else master.data_ptr(),
+                        s1.data_ptr(), s2.data_ptr() if kind == "adam" else None, ctypes.byref(o), one_shot,
+                        0 if one_shot else 1, 0, comm.next_seq(), _lib.current_stream()))
+                    torch.cuda.synchronize()
+                    if not one_shot:                                    # averaged gradient written back everywhere
+                        torch.testing.assert_close(grad.float(), want.to(dtype).float(), **tol)
+                        key = ("grad", str(dtype))
+                        rel = float(((grad.float() - want.to(dtype).float()).abs() / (want.abs() + 1e-3)).max())
+                        worst[key] = max(worst.get(key, 0.0), rel)
+                    ref_p.grad = want.clone()
+                    ref_opt.step()
+                    # Adam divides by sqrt(v) + eps: where |g| is tiny the quotient amplifies the last bit of the
+                    # reduction order, so its parameters are held to an absolute bar of a fraction of one step
+                    ptol = tol if kind == "sgd" else dict(rtol=tol["rtol"], atol=max(tol["atol"], 2e-4))
+                    torch.testing.assert_close(param.float(), ref_p.detach().to(dtype).float(), **ptol)
+                # every rank holds the same parameters, bit for bit
+                mine = param.float().clone()
+                other = mine.clone()
+                dist.broadcast(other, src=0)
+                assert torch.equal(mine, other), "ranks disagree on the updated parameters"
+                comm.check_error()
+                dist.barrier()
+                comm.destroy()
     dist.destroy_process_group()
-    return "ok"
+    return {"%s_%s" % k: v for k, v in worst.items()}
 
 
 def _w_ddp_config1(steps):
@@ -207,19 +252,29 @@ def _w_ddp_syncbn_vs_torch():
         if step == 0:
             # identical weights and inputs: the averaged gradients may differ only by arithmetic
             # (fp32 round-off amplified through 20 BN backward passes), tensor by tensor
+            # (tests/test_gpu_ddp.py::test_per_tensor_grads_against_float64_arbiter measures both implementations
+            # against a float64 run: they are equally far from it, and up to ~1e-2 from each other at the stem)
             for (n, a), b in zip(ref.module.named_parameters(), ours.module.parameters()):
                 err = float((b.grad - a.grad).norm() / (a.grad.norm() + 1e-20))
-                assert err < 2e-2, (n, err)
+                assert err < (1e-3 if n.startswith("fc.") else 2e-2), (n, err)
         o_ref.step(); o_our.step()
         la, lb = float(la.detach()), float(lb.detach())
         assert abs(la - lb) < 1e-2 * la, (step, la, lb)  # north_star: loss curve within 1 %
     torch.testing.assert_close(ours.module.bn1.running_var, ref.module.bn1.running_var, rtol=1e-3, atol=1e-5)
+    # final weights after 8 steps: each tensor has moved by ~8*lr*|g|; the two runs must agree on where it went
+    # to within a small fraction of that distance (and to rtol 1e-3 where the gradients agreed to 1e-4)
+    for (n, a), b, w0 in zip(ref.module.named_parameters(), ours.module.parameters(), base.parameters()):
+        moved = float((a - w0).norm())
+        assert float((b - a).norm()) < 0.05 * moved + 1e-7, (n, float((b - a).norm()), moved)
+    mine = torch.cat([p.detach().reshape(-1) for p in ours.module.parameters()])
+    other = mine.clone(); dist.broadcast(other, src=0)
+    assert torch.equal(mine, other), "replicas diverged"
     dist.barrier()
     dist.destroy_process_group()
     return "ok"
 
 
-def _w_checkpoint():
+def _w_checkpoint(opt_name="sgd"):
     """save_checkpoint of the reference (model.module.state_dict() + optimizer.state_dict() on rank 0,
     01_basic_torch_distributor.py:239-245) with the fused, sharded optimizer: after consolidation the
     checkpoint equals the one a replicated torch SGD writes."""
@@ -236,8 +291,10 @@ def _w_checkpoint():
     ref = torch.nn.parallel.DistributedDataParallel(copy.deepcopy(base), device_ids=[rank])
     ours = b200.prepare_model(copy.deepcopy(base), sync_batchnorm=False, channels_last=False)
     assert isinstance(ours, torch.nn.parallel.DistributedDataParallel) and ours.module is not None
-    o_ref = torch.optim.SGD(ref.parameters(), lr=1e-3, momentum=0.5)
-    o_our = ours.fuse_optimizer(torch.optim.SGD(ours.parameters(), lr=1e-3, momentum=0.5))
+    mk = ((lambda p: torch.optim.SGD(p, lr=1e-3, momentum=0.5)) if opt_name == "sgd"
+          else (lambda p: torch.optim.Adam(p, lr=1e-3)))           # 02_cifar_torch_distributor_resnet.py:213
+    o_ref = mk(ref.parameters())
+    o_our = ours.fuse_optimizer(mk(ours.parameters()))
     for step in range(3):
         gen = torch.Generator().manual_seed(50 * rank + step)
         x, y = torch.randn(32, 3, 32, 32, generator=gen).cuda(), torch.randint(0, 10, (32,), generator=gen).cuda()
@@ -257,17 +314,50 @@ def _w_checkpoint():
         ck = torch.load(blob)
         want_m, want_o = ref.module.state_dict(), o_ref.state_dict()
         assert list(ck["model"]) == list(want_m)
-        for k in want_m:
-            torch.testing.assert_close(ck["model"][k], want_m[k], rtol=1e-5, atol=1e-6)
-        assert ck["optimizer"]["param_groups"][0]["momentum"] == 0.5
-        for idx, st in want_o["state"].items():
-            torch.testing.assert_close(ck["optimizer"]["state"][idx]["momentum_buffer"], st["momentum_buffer"],
-                                       rtol=1e-5, atol=1e-7)
+        if opt_name == "sgd":
+            assert ck["optimizer"]["param_groups"][0]["momentum"] == 0.5
+            for k in want_m:
+                torch.testing.assert_close(ck["model"][k], want_m[k], rtol=1e-5, atol=1e-6)
+            for idx, st in want_o["state"].items():
+                torch.testing.assert_close(ck["optimizer"]["state"][idx]["momentum_buffer"], st["momentum_buffer"],
+                                           rtol=1e-5, atol=1e-7)
+        else:
+            # Adam: a last-bit difference in a near-zero gradient moves a weight by a whole lr in the first
+            # steps, so weights are compared to a fraction of the 3*lr they can have moved; the moments are
+            # smooth in the gradient and must agree closely, `step` exactly
+            for idx, st in want_o["state"].items():
+                got = ck["optimizer"]["state"][idx]
+                assert float(got["step"]) == float(st["step"]) == 3.0
+                torch.testing.assert_close(got["exp_avg"], st["exp_avg"], rtol=1e-3, atol=1e-6)
+                torch.testing.assert_close(got["exp_avg_sq"], st["exp_avg_sq"], rtol=1e-3, atol=1e-9)
+            for k in want_m:
+                if want_m[k].is_floating_point() and "running" not in k:
+                    assert float((ck["model"][k] - want_m[k]).abs().mean()) < 1e-3, k
         # and it loads back into a plain torch model + optimizer (resume path)
         plain = copy.deepcopy(base)
         plain.load_state_dict(ck["model"])
-        po = torch.optim.SGD(plain.parameters(), lr=1e-3, momentum=0.5)
+        po = mk(plain.parameters())
         po.load_state_dict(ck["optimizer"])
+    # resume on every rank: the checkpoint travels from rank 0, goes into a NEW wrapper + fused optimizer, and
+    # training continues in step with the uninterrupted torch run (load_checkpoint, 01_basic_torch_distributor.py:109-119)
+    obj = [ck if rank == 0 else None]
+    dist.broadcast_object_list(obj, src=0)
+    ck = obj[0]
+    torch.manual_seed(99)
+    again = b200.prepare_model(workloads.cifar_resnet18(10).cuda(), sync_batchnorm=False, channels_last=False)
+    o_again = again.fuse_optimizer(mk(again.parameters()))
+    again.module.load_state_dict(ck["model"]); o_again.load_state_dict(ck["optimizer"])
+    for step in range(3, 5):
+        gen = torch.Generator().manual_seed(50 * rank + step)
+        x, y = torch.randn(32, 3, 32, 32, generator=gen).cuda(), torch.randint(0, 10, (32,), generator=gen).cuda()
+        for m, o in ((ref, o_ref), (again, o_again)):
+            o.zero_grad(); F.cross_entropy(m(x), y).backward(); o.step()
+    for (n, a), b in zip(ref.module.named_parameters(), again.module.parameters()):
+        if opt_name == "sgd":
+            torch.testing.assert_close(b, a, rtol=1e-4, atol=1e-6, msg=lambda s: f"{n}: {s}")
+        else:
+            assert float((b - a).abs().mean()) < 1e-3, n
+    again.comm.check_error()
     dist.barrier()
     dist.destroy_process_group()
     return "ok"
@@ -302,26 +392,39 @@ def _w_gather_scalars():
     return "ok"
 
 
-def test_all_gather_scalars_two_ranks():
-    assert TorchDistributor(num_processes=2).run(_w_gather_scalars) == "ok"
+@pytest.mark.parametrize("world", WORLDS)
+def test_all_gather_scalars(world):
+    assert TorchDistributor(num_processes=world).run(_w_gather_scalars) == "ok"
 
 
-def test_checkpoint_round_trip_two_ranks():
-    assert TorchDistributor(num_processes=2).run(_w_checkpoint) == "ok"
+@pytest.mark.parametrize("opt", ["sgd", "adam"])
+@pytest.mark.parametrize("world", WORLDS)
+def test_checkpoint_round_trip(world, opt):
+    assert TorchDistributor(num_processes=world).run(_w_checkpoint, opt) == "ok"
 
 
-def test_syncbn_two_ranks():
-    assert TorchDistributor(num_processes=2).run(_w_syncbn) == "ok"
+@pytest.mark.parametrize("world", WORLDS)
+def test_syncbn_against_torch_syncbn(world):
+    out = TorchDistributor(num_processes=world).run(_w_syncbn)
+    print(f"\n[parity world={world}] SyncBN vs nn.SyncBatchNorm+NCCL, max abs difference: {out}")
+    assert out["y_torch.float32"] < 1e-4 and out["dx_torch.float32"] < 1e-3
 
 
-def test_fused_allreduce_update_two_ranks():
-    assert TorchDistributor(num_processes=2).run(_w_allreduce) == "ok"
+@pytest.mark.parametrize("world", WORLDS)
+def test_fused_allreduce_update_against_nccl(world):
+    out = TorchDistributor(num_processes=world).run(_w_allreduce)
+    print(f"\n[parity world={world}] fused all-reduce vs NCCL all-reduce, max relative difference: {out}")
+    assert out["grad_torch.float32"] < 1e-5
 
 
 def test_config1_loss_curve_two_ranks():
+    if _ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
     out = TorchDistributor(num_processes=2).run(_w_ddp_config1, 200)
+    print(f"\n[parity world=2] config 1, 200 steps vs stock DDP golden: {out}")
     assert out["max_rel"] < 0.01
 
 
-def test_syncbn_ddp_against_torch_two_ranks():
-    assert TorchDistributor(num_processes=2).run(_w_ddp_syncbn_vs_torch) == "ok"
+@pytest.mark.parametrize("world", WORLDS)
+def test_syncbn_ddp_against_torch(world):
+    assert TorchDistributor(num_processes=world).run(_w_ddp_syncbn_vs_torch) == "ok"

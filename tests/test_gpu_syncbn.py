@@ -13,6 +13,21 @@ pytestmark = pytest.mark.gpu
 TOL = {torch.float32: dict(rtol=1e-4, atol=1e-5), torch.bfloat16: dict(rtol=2e-2, atol=2e-2)}
 
 
+@pytest.fixture(autouse=True, params=["two_kernels", "one_kernel_cs16", "one_kernel_cs8"])
+def bn_path(request):
+    """Every test of this file runs through both code paths of b200dp_bn_forward / _backward: the statistics
+    (reduce) kernel followed by the apply kernel, and the single cluster kernel that small layers take (with
+    clusters of 16 CTAs and of 8).  The library's defaults come back afterwards."""
+    from dbx_distributed_pytorch_examples_b200 import _lib
+    lib = _lib.lib()
+    if request.param == "two_kernels":
+        lib.b200dp_bn_set_one_kernel_limits(0, 0, -1)
+    else:
+        lib.b200dp_bn_set_one_kernel_limits(1 << 20, 1 << 20, 16 if request.param.endswith("16") else 8)
+    yield request.param
+    lib.b200dp_bn_set_one_kernel_limits(56, 40, 16)
+
+
 def rows(t):
     C = t.shape[1]
     return t.detach().float().permute(0, 2, 3, 1).reshape(-1, C).cpu().numpy()
@@ -50,15 +65,19 @@ def test_against_oracle(dtype, shape, mode):
     np.testing.assert_allclose(bn.running_mean.cpu().numpy(), rm_new, rtol=1e-5, atol=1e-6)
     np.testing.assert_allclose(bn.running_var.cpu().numpy(), rv_new, rtol=1e-4, atol=1e-6)
     assert int(bn.num_batches_tracked) == 1
-    # the backward oracle takes the mask from OUR y (bf16 rounding can move values across 0)
-    dxs, drs, gws, gbs = syncbn_ref.backward([rows(dy)], [rows(x)], [rows(y)], w.cpu().numpy(), mean, invstd, relu)
+    # The backward oracle takes the ReLU mask from ITS OWN y.  Where that y is within rounding of zero
+    # the sign is not a property of the input, so those few elements are left out of the element-wise
+    # comparison (they still enter the sums on both sides; the tolerance covers a flipped one).
+    dxs, drs, gws, gbs = syncbn_ref.backward([rows(dy)], [rows(x)], [ys[0]], w.cpu().numpy(), mean, invstd, relu)
+    sure = (np.abs(ys[0]) > (2.0 ** -7 if dtype == torch.bfloat16 else 1e-5) * np.maximum(1.0, np.abs(rows(x)))) | (not relu)
+    assert sure.mean() > 0.4
     scale = max(1.0, float(np.abs(dxs[0]).max()))
-    np.testing.assert_allclose(rows(dx), dxs[0], rtol=tol["rtol"], atol=tol["atol"] * scale)
+    np.testing.assert_allclose(np.where(sure, rows(dx), 0), np.where(sure, dxs[0], 0), rtol=tol["rtol"], atol=tol["atol"] * scale)
     gtol = dict(rtol=2e-3, atol=2e-3 * N * H * W ** 0.5) if dtype == torch.float32 else dict(rtol=3e-2, atol=0.5)
     np.testing.assert_allclose(bn.weight.grad.cpu().numpy(), gws[0], **gtol)
     np.testing.assert_allclose(bn.bias.grad.cpu().numpy(), gbs[0], **gtol)
-    if use_res:
-        np.testing.assert_allclose(rows(dres), drs[0], **tol)  # d_residual is the masked dy
+    if use_res:  # d_residual is the masked dy
+        np.testing.assert_allclose(np.where(sure, rows(dres), 0), np.where(sure, drs[0], 0), **tol)
 
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
@@ -84,6 +103,78 @@ def test_against_torch_batch_norm(dtype):
         torch.testing.assert_close(dx, xr.grad, rtol=1e-3, atol=1e-4)
         torch.testing.assert_close(bn.weight.grad, wr.grad, rtol=1e-3, atol=1e-2)
         torch.testing.assert_close(bn.bias.grad, br.grad, rtol=1e-3, atol=1e-2)
+    else:
+        # bf16 against torch's OWN bf16 batch norm (cuDNN / ATen NHWC kernels, bf16 in and out) fed the same
+        # bits: both round a float32 result to bf16 once, so they may differ by one bf16 ulp of the value
+        xb = x.clone().requires_grad_(True)
+        wb, bb = w.clone().requires_grad_(True), b.clone().requires_grad_(True)
+        yb = torch.relu(F.batch_norm(xb, rm.clone(), rv.clone(), wb, bb, True, 0.1, 1e-5))
+        yb.backward(dy)
+        torch.testing.assert_close(y, yb, rtol=2 ** -7, atol=2 ** -7)
+        agree = (y > 0) == (yb > 0)        # an element whose ReLU fell on the other side has another gradient
+        assert float(agree.float().mean()) > 0.999
+        torch.testing.assert_close(torch.where(agree, dx, 0), torch.where(agree, xb.grad, 0), rtol=2e-2, atol=2e-2)
+        torch.testing.assert_close(bn.weight.grad, wb.grad.float(), rtol=2e-2, atol=0.5)
+        torch.testing.assert_close(bn.bias.grad, bb.grad.float(), rtol=2e-2, atol=0.5)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_extreme_statistics(dtype):
+    """Channels a one-pass variance gets wrong: |mean| / std = 257 (in bf16 the values 256 and 258 are
+    neighbours: nothing narrower can be stored around that mean), a constant channel (variance exactly 0:
+    invstd = 1/sqrt(eps), y = bias, dx = 0) and a large constant one.  Against float64 on the same bits."""
+    torch.manual_seed(11)
+    N, C, H, W = 64, 64, 16, 16
+    x = torch.randn(N, C, H, W, device="cuda")
+    x[:, 0] = 256.0 + 2.0 * torch.randint(0, 2, (N, H, W), device="cuda")       # mean 257, std 1
+    x[:, 1] = 3.0                                                              # constant
+    x[:, 2] = -1024.0                                                          # constant, large
+    x[:, 3] = 0.0
+    x[:, 4] = 4096.0 + 32.0 * torch.randint(0, 2, (N, H, W), device="cuda")    # the same ratio, larger scale
+    x = x.to(dtype).contiguous(memory_format=torch.channels_last)
+    dy = torch.randn(N, C, H, W, device="cuda").to(dtype).contiguous(memory_format=torch.channels_last)
+    w, b = torch.rand(C, device="cuda") + 0.5, torch.randn(C, device="cuda")
+    bn, y, dx, _ = run_ours(x, None, dy, w, b, torch.zeros(C, device="cuda"), torch.ones(C, device="cuda"), False)
+    x64 = x.double()
+    mean = x64.mean((0, 2, 3)); var = x64.var((0, 2, 3), unbiased=False)
+    n = N * H * W
+    torch.testing.assert_close(bn.running_mean.double(), 0.1 * mean, rtol=1e-6, atol=1e-7)
+    torch.testing.assert_close(bn.running_var.double(), 0.9 + 0.1 * var * n / (n - 1), rtol=2e-3, atol=1e-6)
+    assert float(bn.running_var[1]) == pytest.approx(0.9, abs=1e-6) and float(bn.running_var[2]) == pytest.approx(0.9, abs=1e-3)
+    want = (x64 - mean.view(1, -1, 1, 1)) / torch.sqrt(var + 1e-5).view(1, -1, 1, 1) * w.double().view(1, -1, 1, 1) \
+        + b.double().view(1, -1, 1, 1)
+    tol = dict(rtol=1e-3, atol=2e-3) if dtype == torch.float32 else dict(rtol=2e-2, atol=2e-2)
+    torch.testing.assert_close(y.double()[:, [0, 4]], want[:, [0, 4]], **tol)   # the high-ratio channels
+    torch.testing.assert_close(y.double()[:, 5:], want[:, 5:], **tol)
+    for c in (1, 3):   # constant channels: y is the bias, the gradient vanishes (the sum term cancels dy's mean only)
+        torch.testing.assert_close(y[:, c].float(), b[c].expand(N, H, W).to(dtype).float(), rtol=0, atol=1e-2)
+    assert torch.isfinite(dx.float()).all() and torch.isfinite(y.float()).all()
+
+
+def test_single_layer_gradient_error_against_float64():
+    """The backward of ONE layer, ours and torch's float32 kernels, each against torch's float64 batch norm on
+    the same (x, dy): the float32 implementations must be equally far from the truth.  (The whole-model
+    version of this measurement is in test_gpu_ddp.py.)"""
+    torch.manual_seed(12)
+    for shape in [(128, 64, 32, 32), (128, 512, 4, 4), (32, 256, 14, 14)]:
+        C = shape[1]
+        x = (torch.randn(shape, device="cuda") * 1.5 + 0.3).contiguous(memory_format=torch.channels_last)
+        dy = torch.randn(shape, device="cuda").contiguous(memory_format=torch.channels_last)
+        w, b = torch.rand(C, device="cuda") + 0.5, torch.randn(C, device="cuda")
+        bn, y, dx, _ = run_ours(x, None, dy, w, b, torch.zeros(C, device="cuda"), torch.ones(C, device="cuda"), False)
+        outs = {}
+        for name, dt in (("f64", torch.float64), ("f32", torch.float32)):
+            xr = x.to(dt).requires_grad_(True)
+            wr, br = w.to(dt).requires_grad_(True), b.to(dt).requires_grad_(True)
+            yr = F.batch_norm(xr, None, None, wr, br, True, 0.1, 1e-5)
+            yr.backward(dy.to(dt))
+            outs[name] = (yr.detach().double(), xr.grad.double(), wr.grad.double(), br.grad.double())
+        ours = (y.double(), dx.double(), bn.weight.grad.double(), bn.bias.grad.double())
+        for k, what in enumerate(("y", "dx", "dweight", "dbias")):
+            ref = outs["f64"][k]
+            e_ours = float((ours[k] - ref).norm() / ref.norm())
+            e_torch = float((outs["f32"][k] - ref).norm() / ref.norm())
+            assert e_ours <= 2.0 * e_torch + 2e-7, (shape, what, e_ours, e_torch)
 
 
 def test_mask_word_mode_equals_mask_from_y(monkeypatch):

@@ -32,10 +32,19 @@ def main():
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--warm", action="store_true")
     ap.add_argument("--dtype", default="bf16")
+    ap.add_argument("--mask-mode", type=int, default=2, choices=[2, 3],
+                    help="backward of residual layers: 2 = ReLU mask from y (the default in training), 3 = from mask words")
+    ap.add_argument("--one-kernel-mb", type=int, nargs=2, default=None, metavar=("FWD", "BWD"),
+                    help="size limits of the one-kernel path for the '(1 call)' columns (0 0 = always two kernels)")
+    ap.add_argument("--cluster", type=int, default=-1, help="cluster size of the one-kernel path (8 or 16)")
     a = ap.parse_args()
     peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(
         os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
     lib = _lib.lib()
+    if a.one_kernel_mb is not None or a.cluster > 0:
+        f, b_ = a.one_kernel_mb if a.one_kernel_mb is not None else (-1, -1)
+        lib.b200dp_bn_set_one_kernel_limits(f, b_, a.cluster)
+    print(f"# one-kernel limits: {a.one_kernel_mb} cluster {a.cluster} mask mode {a.mask_mode} {'warm' if a.warm else 'cold'}")
     dt = torch.bfloat16 if a.dtype == "bf16" else torch.float32
     code, es = _lib.dtype_code(dt), (2 if dt == torch.bfloat16 else 4)
     dev = torch.device("cuda")
@@ -55,26 +64,27 @@ def main():
         stats = torch.empty(2 * C + 1, device=dev)
         save = torch.empty(2 * C + 1, device=dev)
         sums, gw, gb = torch.empty(2 * C, device=dev), torch.empty(C, device=dev), torch.empty(C, device=dev)
-        mode = 3 if res else 1
-        mk = torch.empty(M * C // 8, dtype=torch.int32, device=dev) if res else None
+        mode = a.mask_mode if res else 1
+        mk = torch.empty(M * C // 8, dtype=torch.int32, device=dev) if (res and mode == 3) else None
+        mfrac = {2: 1.0, 3: 0.25}[a.mask_mode]
         P = lambda t: 0 if t is None else t.data_ptr()  # noqa: E731
         calls = {
             "stats": (lambda: lib.b200dp_bn_fwd_stats(P(x), code, M, C, P(scratch), P(stats), None, 0, s), M * C * es),
             "fwd_apply": (lambda: lib.b200dp_bn_fwd_apply(P(x), P(r), P(y), code, M, C, P(stats), P(w), P(b), 1e-5, 0.1,
                                                          None, None, P(save), P(save) + 4 * C, P(save) + 8 * C, 1, None, 0, s, P(mk)),
-                          M * C * es * (3.25 if res else 2)),
-            "bwd_reduce": (lambda: lib.b200dp_bn_bwd_reduce(P(dy), P(x), P(mk if res else y), code, M, C, P(save), P(save) + 4 * C, P(w), P(b),
+                          M * C * es * (3 + (0.25 if mk is not None else 0) if res else 2)),
+            "bwd_reduce": (lambda: lib.b200dp_bn_bwd_reduce(P(dy), P(x), P(mk if mk is not None else y), code, M, C, P(save), P(save) + 4 * C, P(w), P(b),
                                                            mode, P(scratch), P(sums), P(gw), P(gb), None, 0, s),
-                           M * C * es * (2.25 if res else 2)),
-            "bwd_apply": (lambda: lib.b200dp_bn_bwd_apply(P(dy), P(x), P(mk if res else y), P(dx), P(dr), code, M, C, P(save), P(save) + 4 * C,
+                           M * C * es * (2 + mfrac if res else 2)),
+            "bwd_apply": (lambda: lib.b200dp_bn_bwd_apply(P(dy), P(x), P(mk if mk is not None else y), P(dx), P(dr), code, M, C, P(save), P(save) + 4 * C,
                                                          P(w), P(b), P(sums), P(save) + 8 * C, mode, None, 0, s),
-                          M * C * es * (4.25 if res else 3)),
+                          M * C * es * (4 + mfrac if res else 3)),
         }
         nb = lambda k: calls[k][1]  # noqa: E731
         calls["fwd(1 call)"] = (lambda: lib.b200dp_bn_forward(P(x), P(r), P(y), code, M, C, P(scratch), P(stats), P(w), P(b),
                                                              1e-5, 0.1, None, None, P(save), 1, None, 0, s, P(mk), None),
                                 nb("stats") + nb("fwd_apply"))
-        calls["bwd(1 call)"] = (lambda: lib.b200dp_bn_backward(P(dy), P(x), P(mk if res else y), P(dx), P(dr), code, M, C, P(save), P(w), P(b),
+        calls["bwd(1 call)"] = (lambda: lib.b200dp_bn_backward(P(dy), P(x), P(mk if mk is not None else y), P(dx), P(dr), code, M, C, P(save), P(w), P(b),
                                                               mode, P(scratch), P(sums), P(gw), P(gb), None, 0, s),
                                 nb("bwd_reduce") + nb("bwd_apply"))
         cells = []
