@@ -63,9 +63,31 @@ def build(force: bool = False, verbose: bool = False) -> str:
         raise B200DPError("nvcc failed:\n" + proc.stdout + proc.stderr)
     if verbose:
         print(proc.stderr)
+    check_sass(LIB_PATH)
     build_fastcall(force=True)
     build_autograd(force=True)
     return LIB_PATH
+
+
+def check_sass(path: str) -> None:
+    """Refuse a build that contains the one miscompilation met so far: ptxas 12.9 turned the cp.async ring of
+    `bn_bwd_apply_kernel<float, *>` into `LDGSTS [R+UR0], desc[UR1]` with the uniform operands never
+    written, which B200 answers with "illegal instruction" (csrc/bn.cu, RowRing::init has the workaround)."""
+    import re
+    import shutil
+
+    tool = shutil.which("cuobjdump") or os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "bin", "cuobjdump")
+    if not os.path.exists(tool):
+        return
+    proc = subprocess.run([tool, "-sass", path], capture_output=True, text=True, stdin=subprocess.DEVNULL, timeout=600)
+    bad, fn = {}, "?"
+    for line in proc.stdout.splitlines():
+        if "Function :" in line:
+            fn = line.split()[-1]
+        elif "LDGSTS" in line and re.search(r"\[R\d+\+UR|desc\[UR[01]\]", line):
+            bad[fn] = bad.get(fn, 0) + 1
+    if bad:
+        raise B200DPError("the build contains LDGSTS instructions with unset uniform operands in: " + ", ".join(sorted(bad)))
 
 
 def _fast_path() -> str:
@@ -184,6 +206,8 @@ _SIGNATURES = {
     "b200dp_bn_backward": (c_int, [_VP, _VP, _VP, _VP, _VP, c_int, c_int64, c_int, _VP, _VP, _VP, c_int, _VP, _VP,
                                    _VP, _VP, _VP, c_uint32, _VP]),
     "b200dp_comm_create": (c_int, [c_int, c_int, c_size_t, POINTER(_VP)]),
+    "b200dp_comm_create_external": (c_int, [c_int, c_int, c_size_t, POINTER(_VP), _VP, POINTER(_VP)]),
+    "b200dp_comm_has_multicast": (c_int, [_VP]),
     "b200dp_comm_export": (c_int, [_VP, _VP]),
     "b200dp_comm_open_peers": (c_int, [_VP, _VP]),
     "b200dp_comm_destroy": (c_int, [_VP]),
@@ -197,7 +221,7 @@ _SIGNATURES = {
     "b200dp_comm_error": (c_int, [_VP]),
     "b200dp_comm_error_async": (c_int, [_VP, _VP, _VP]),
     "b200dp_bn_one_kernel": (c_int, [c_int, c_int64, c_int, c_int]),
-    "b200dp_bn_set_one_kernel_limits": (c_int, [c_int, c_int, c_int]),
+    "b200dp_bn_set_one_kernel_limits": (c_int, [c_int, c_int, c_int, c_int]),
     "b200dp_bucket_pack": (c_int, [POINTER(_VP), POINTER(c_int64), POINTER(c_int64), c_int, _VP,
                                    c_int, c_float, _VP]),
     "b200dp_allreduce_update": (c_int, [_VP, c_size_t, c_int, c_size_t, c_int, c_int64, c_int64,

@@ -82,14 +82,16 @@ Grid2 plan_grid_clustered(int64_t M, int C, int max_clusters) {
   return g;
 }
 
-// cudaOccupancyMaxActiveClusters for a kernel of this file with clusters of `cs` CTAs, asked once per
-// (kernel, device, cluster size).  Forward runs on the caller's thread and backward on autograd's, so the
-// small cache is guarded.  Returns 0 when the runtime cannot place such a cluster at all.
+// cudaOccupancyMaxActiveClusters for a kernel of this file with clusters of `cs` CTAs of `threads` threads
+// and `dyn_smem` bytes of dynamic shared memory, asked once per (kernel, device, cluster size).  Forward runs
+// on the caller's thread and backward on autograd's, so the small cache is guarded.  Returns 0 when the
+// runtime cannot place such a cluster at all.  Also opts the kernel in to what the launch will need
+// (cluster sizes above 8, more than 48 KB of dynamic shared memory).
 std::mutex g_occ_mutex;
 template <typename KernelT>
-int max_active_clusters(KernelT kernel, int cs = kCluster) {
+int max_active_clusters(KernelT kernel, int cs = kCluster, int threads = kT, int dyn_smem = 0) {
   struct Entry { const void* fn; int dev; int cs; int n; };
-  static Entry table[512];
+  static Entry table[1024];
   static int used = 0;
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess) return 64;
@@ -100,10 +102,13 @@ int max_active_clusters(KernelT kernel, int cs = kCluster) {
   if (cs > 8) {  // clusters of more than 8 CTAs are an opt-in per kernel
     if (cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) cudaGetLastError();
   }
+  if (dyn_smem > 48 * 1024) {
+    if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_smem) != cudaSuccess) cudaGetLastError();
+  }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(cs * B200DP_NUM_SMS, 1, 1);
-  cfg.blockDim = dim3(kT, 1, 1);
-  cfg.dynamicSmemBytes = 0;
+  cfg.blockDim = dim3(threads, 1, 1);
+  cfg.dynamicSmemBytes = dyn_smem;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = cs;
@@ -114,9 +119,9 @@ int max_active_clusters(KernelT kernel, int cs = kCluster) {
   int n = 0;
   if (cudaOccupancyMaxActiveClusters(&n, kernel, &cfg) != cudaSuccess || n <= 0) {
     cudaGetLastError();
-    n = cs == kCluster ? 64 : 0;  // the portable size: be conservative (8 per GPC); larger ones: not available
+    n = (cs == kCluster && threads == kT) ? 64 : 0;  // the two-kernel path: be conservative (8 per GPC); else: not available
   }
-  if (used < 512) {
+  if (used < 1024) {
     table[used].fn = key;
     table[used].dev = dev;
     table[used].cs = cs;
@@ -339,14 +344,14 @@ constexpr int kChunkMax = kCV * 8;                 // channels per chunk at most
 constexpr int kXrStride = 2 * kChunkMax + 4;       // floats per rank in the gathered copy
 
 // The whole CTA stores the staged vector into every rank's slot: world * (cw + 1) stores spread over
-// its 256 threads (before: 8 threads issuing 17 scalar stores per peer, back to back).
+// its threads (before: 8 threads issuing 17 scalar stores per peer, back to back).
 __device__ __forceinline__ void push_chunk(const b200dp_peers& P, uint32_t seq, int C, int cb, int cw,
                                            const float* stage) {
   const int slot = seq % B200DP_XCHG_SLOTS;
   const int valid = (C - cb < cw) ? C - cb : cw;  // multiple of 4: whole pairs
   const int pairs = valid >> 1;
   const int units = 2 * pairs + 1;
-  for (int u = threadIdx.x; u < P.world * units; u += kT) {
+  for (int u = threadIdx.x; u < P.world * units; u += blockDim.x) {
     const int p = u / units;
     int j = u - p * units;
     uint2* d = P.sync[p]->bn_ll[slot][P.rank];
@@ -363,7 +368,7 @@ __device__ __forceinline__ void push_chunk(const b200dp_peers& P, uint32_t seq, 
 
 // The whole CTA polls the ranks' words of this chunk in its own sync area (the peers stored them there)
 // and leaves them in shared memory: xr[rank * kXrStride + ...] = a[cw] | b[cw] | cnt.  At most
-// ceil(world * (cw + 1) / 256) polls per thread, side by side (before: 17 one after the other).
+// ceil(world * (cw + 1) / blockDim.x) polls per thread, side by side (before: 17 one after the other).
 __device__ __forceinline__ void wait_and_gather(const b200dp_peers& P, uint32_t seq, int C, int cb, int cw,
                                                 float* xr) {
   const int slot = seq % B200DP_XCHG_SLOTS;
@@ -371,7 +376,7 @@ __device__ __forceinline__ void wait_and_gather(const b200dp_peers& P, uint32_t 
   const int pairs = valid >> 1;
   const int units = 2 * pairs + 1;
   bool ok = true;
-  for (int u = threadIdx.x; u < P.world * units; u += kT) {
+  for (int u = threadIdx.x; u < P.world * units; u += blockDim.x) {
     const int p = u / units;
     int j = u - p * units;
     const uint2* d = P.sync[P.rank]->bn_ll[slot][p];
@@ -438,15 +443,23 @@ __device__ __forceinline__ RowRange my_rows(int64_t M, int r) {
   return rr;
 }
 
-template <int D, int NS, bool EVICT_FIRST, bool W2 = false>  // W2: stream 2 carries one 32-bit word per row
+template <int D, int NS, bool EVICT_FIRST, bool W2 = false, int NT = kT>  // W2: stream 2 carries one 32-bit word per row; NT: threads per CTA
 struct RowRing {
   uint32_t base;  // shared-space address of this thread's slot (stream 0, depth 0)
   uint64_t pol;
   __device__ __forceinline__ void init(void* smem) {
     base = (uint32_t)__cvta_generic_to_shared(smem) + threadIdx.x * 16;
+    // Keep the slot address in ONE ordinary register.  Left to itself ptxas 12.9 may split it into a
+    // uniform shared-window base plus a per-thread offset and emit LDGSTS [R+UR], desc[UR] with the
+    // uniform operands unset (seen in bn_bwd_apply_kernel<float, *>): the GPU raises "illegal instruction".
+    // (An identity shuffle: the value is unchanged, but the compiler can no longer prove which part of it
+    // is uniform across the warp.)
+    // init() may run under a divergent branch (threads past the last channel skip it): only the lanes
+    // that are here take part.
+    base = __shfl_sync(__activemask(), base, threadIdx.x & 31);
     if (EVICT_FIRST) pol = evict_first_policy();
   }
-  __device__ __forceinline__ uint32_t slot(int d, int s) const { return base + (s * D + d) * (kT * 16); }
+  __device__ __forceinline__ uint32_t slot(int d, int s) const { return base + (s * D + d) * (NT * 16); }
   __device__ __forceinline__ void issue(int d, const void* p0, const void* p1, const void* p2) {
     if (EVICT_FIRST) {
       cp_async16_evict_first(slot(d, 0), p0, pol);
@@ -494,7 +507,7 @@ struct RowRing {
     }
     cp_async_wait<0>();
   }
-  static constexpr int kBytes = D * NS * kT * 16;
+  static constexpr int kBytes = D * NS * NT * 16;
 };
 
 
@@ -1082,29 +1095,76 @@ __global__ void __launch_bounds__(kT, kOccBwd) bn_bwd_apply_kernel(const __grid_
 // (or the backward sums), folds them over its CTAs through distributed shared memory — hardware
 // co-schedules the CTAs of a cluster, so that wait cannot starve whatever else runs on the GPU, which a
 // grid-wide spin could — exchanges them across ranks, and streams the rows a second time to apply,
-// this time out of the L2 they were just read into.  Chunks are narrow (2, 4 or 8 sixteen-byte vectors
-// per row instead of 8) so that even C = 128 gives enough clusters to fill the GPU.
-constexpr int kFusedMaxCS = 16;      // CTAs per cluster (16 is an opt-in size; 8 when the device refuses it)
-constexpr int kFusedMaxGroups = 64;  // cluster size x vectors per row chunk at most (bounds the DSMEM exchange buffer)
+// this time out of the L2 they were just read into.
+//
+// Geometry.  A cluster has at most 16 CTAs and there is one cluster per chunk, so the GPU is filled with
+// LARGE CTAs (1024 threads forward, 768 backward: one per SM, with the same 8-9 rows of 16 bytes in
+// flight per thread as the two-kernel path, i.e. the same ~100 KB per SM outstanding) and chunks of 2, 4
+// or 8 sixteen-byte vectors per row, chosen so that chunks x cluster size comes close to the SM count.
+constexpr int kFusedMaxCS = 16;          // CTAs per cluster (sizes above 8 are an opt-in per kernel)
+constexpr int kFusedMaxGroups = 128;     // cluster size x vectors per row chunk at most
+constexpr int kFwdThreads = 1024;
+constexpr int kBwdThreads = 768;
 
 struct FusedGeom {
   int cvw;   // 16-byte vectors per row chunk (2, 4, 8)
-  int cs;    // cluster size = row splits
-  int rev2;  // second pass walks the rows last -> first (most recently read first)
+  int cs;    // cluster size = row splits of the chunk
+  int rev2;  // second pass walks the rows last -> first
 };
 
-// Every CTA of the cluster hands its partial (threads tid < cvw) to every CTA, itself included; after the
-// cluster barrier each folds the cs partials in CTA order, so all of them hold bit-identical results.
-// mine: smem [cvw * W]; xchg: smem [kFusedMaxGroups * W], written remotely.
+// `nsrc` (<= 32) partials of channel group cv lie in shared memory at src[(l * cvw + cv) * W], l < nsrc.
+// Warp cv (cv < cvw) folds them with a shuffle tree; lane 0 of that warp ends up with the result.
+template <int N, bool WELFORD>
+__device__ __forceinline__ void tree_fold(int cvw, int nsrc, const float* src, float& n, float* a, float* b) {
+  constexpr int W = 2 * N + 1;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (w >= cvw) return;
+  n = 0.f;
+#pragma unroll
+  for (int k = 0; k < N; ++k) a[k] = b[k] = 0.f;
+  if (lane < nsrc) {
+    const float* s = src + (lane * cvw + w) * W;
+#pragma unroll
+    for (int k = 0; k < N; ++k) {
+      a[k] = s[k];
+      b[k] = s[N + k];
+    }
+    n = s[2 * N];
+  }
+  warp_fold<N, WELFORD>(1, n, a, b);
+}
+
+// Rows of a CTA -> lane 0 of warps 0 .. cvw-1.  wp: shared memory, (blockDim.x / 32) * cvw * W floats.
+template <int N, bool WELFORD>
+__device__ __forceinline__ void cta_fold_big(int cvw, float* wp, float& n, float* a, float* b) {
+  constexpr int W = 2 * N + 1;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  warp_fold<N, WELFORD>(cvw, n, a, b);
+  if (lane < cvw) {
+    float* d = wp + (w * cvw + lane) * W;
+#pragma unroll
+    for (int k = 0; k < N; ++k) {
+      d[k] = a[k];
+      d[N + k] = b[k];
+    }
+    d[2 * N] = n;
+  }
+  __syncthreads();
+  tree_fold<N, WELFORD>(cvw, blockDim.x >> 5, wp, n, a, b);
+}
+
+// Every CTA of the cluster hands its partial (lane 0 of warps < cvw) to every CTA, itself included; after
+// the cluster barrier each folds the cs partials with the same tree, so all hold bit-identical results
+// (again in lane 0 of warps < cvw).  mine: smem [cvw * W]; xchg: smem [cs * cvw * W], written remotely.
 template <int N, bool WELFORD>
 __device__ __forceinline__ void cluster_fold(int cvw, int cs, float* mine, float* xchg, float& n, float* a,
                                              float* b, cg::cluster_group::arrival_token&& started) {
   constexpr int W = 2 * N + 1;
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   cg::cluster_group cluster = cg::this_cluster();
   const unsigned rank = cluster.block_rank();
-  if (tid < cvw) {
-    float* d = mine + tid * W;
+  if (lane == 0 && w < cvw) {
+    float* d = mine + w * W;
 #pragma unroll
     for (int k = 0; k < N; ++k) {
       d[k] = a[k];
@@ -1115,35 +1175,13 @@ __device__ __forceinline__ void cluster_fold(int cvw, int cs, float* mine, float
   __syncthreads();
   cluster.barrier_wait(std::move(started));  // every CTA of the cluster has started: its shared memory exists
   const int per = cvw * W;
-  for (int it = tid; it < cs * per; it += kT) {
+  for (int it = tid; it < cs * per; it += blockDim.x) {
     const int q = it / per, e = it - q * per;
     float* dst = cluster.map_shared_rank(xchg + rank * per + e, q);
     *dst = mine[e];
   }
   cluster.sync();  // release / acquire at cluster scope
-  if (tid < cvw) {
-    n = 0.f;
-#pragma unroll
-    for (int k = 0; k < N; ++k) a[k] = b[k] = 0.f;
-    for (int q = 0; q < cs; ++q) {
-      const float* src = xchg + q * per + tid * W;
-      float oa[N], ob[N];
-#pragma unroll
-      for (int k = 0; k < N; ++k) {
-        oa[k] = src[k];
-        ob[k] = src[N + k];
-      }
-      if (WELFORD) {
-        welford_merge<N>(n, a, b, src[2 * N], oa, ob);
-      } else {
-#pragma unroll
-        for (int k = 0; k < N; ++k) {
-          a[k] += oa[k];
-          b[k] += ob[k];
-        }
-      }
-    }
-  }
+  tree_fold<N, WELFORD>(cvw, cs, xchg, n, a, b);
 }
 
 struct FusedRows {
@@ -1158,24 +1196,25 @@ __device__ __forceinline__ FusedRows fused_rows(int64_t M, int r, int rp, int cs
   return rr;
 }
 
-constexpr int kFusedRingBytes = 36 * 1024;  // the largest ring any phase uses (3 streams x 3 deep)
+extern __shared__ __align__(16) unsigned char fused_dyn_smem[];  // the rings of the one-kernel path
 
 template <typename T, bool RELU, bool RES>
-__global__ void __launch_bounds__(kT, kOccFwd)
+__global__ void __launch_bounds__(kFwdThreads, 1)
 bn_fwd_fused_kernel(const __grid_constant__ FwdArgs A, const FusedGeom G, const __grid_constant__ b200dp_peers P,
                     uint32_t seq) {
   constexpr int N = Vec<T>::N;
   constexpr int W = 2 * N + 1;
-  using Ring1 = RowRing<8, 1, false>;
-  using Ring2 = RowRing<RES ? 4 : 8, RES ? 2 : 1, true>;
-  __shared__ __align__(16) unsigned char smem[Ring1::kBytes];  // rings, then the warp partials of the fold
+  constexpr int NT = kFwdThreads;
+  using Ring1 = RowRing<8, 1, false, false, NT>;
+  using Ring2 = RowRing<RES ? 4 : 8, RES ? 2 : 1, true, false, NT>;
+  static_assert(Ring2::kBytes <= Ring1::kBytes, "ring");
+  unsigned char* smem = fused_dyn_smem;  // Ring1::kBytes: the rings, and in between the warp partials of the fold
   __shared__ __align__(16) float xchg[kFusedMaxGroups * W];
-  __shared__ __align__(16) float mine[2 * kChunkMax + 8];       // partial for the cluster, then the exchange stage
+  __shared__ __align__(16) float mine[2 * kChunkMax + 8];  // partial for the cluster, then the exchange stage
   __shared__ __align__(16) float coef[3][kChunkMax];
   __shared__ __align__(16) float xr[B200DP_MAX_WORLD * kXrStride];
-  static_assert(Ring2::kBytes <= Ring1::kBytes, "ring");
-  const int tid = threadIdx.x;
-  const int cvw = G.cvw, cs = G.cs, rp = kT / cvw;
+  const int tid = threadIdx.x, lane = tid & 31, wrp = tid >> 5;
+  const int cvw = G.cvw, cs = G.cs, rp = NT / cvw;
   const int cv = tid % cvw, r = tid / cvw;
   const int C = A.C;
   const int cw = cvw * N, cb = blockIdx.y * cw;
@@ -1241,9 +1280,11 @@ bn_fwd_fused_kernel(const __grid_constant__ FwdArgs A, const FusedGeom G, const 
     }
   }
   __syncthreads();  // rings drained: the fold may use the memory
-  cta_fold<N, true>(cvw, reinterpret_cast<float*>(smem), n, mean, m2);
+  cta_fold_big<N, true>(cvw, reinterpret_cast<float*>(smem), n, mean, m2);
   cluster_fold<N, true>(cvw, cs, mine, xchg, n, mean, m2, std::move(started));
-  // threads tid < cvw of every CTA now hold this rank's (n, mean, M2) of their channel group
+  // lane 0 of warps < cvw of every CTA now holds this rank's (n, mean, M2) of channel group `wrp`
+  const bool holder = lane == 0 && wrp < cvw;
+  const int hc0 = cb + wrp * N;  // the holder's first channel
 
   // second pass: start the rows flying before the coefficients are worked out
   const bool rev = G.rev2 != 0;
@@ -1254,44 +1295,44 @@ bn_fwd_fused_kernel(const __grid_constant__ FwdArgs A, const FusedGeom G, const 
     p1 = RES ? (const void*)(rb + off2 + k * step2) : nullptr;
     p2 = nullptr;
   };
-  __syncthreads();  // the fold is done with smem
+  __syncthreads();  // the fold is done with the ring memory
   Ring2 ring2;
   ring2.init(smem);
   ring2.prime(nrows, ptrs2);
 
   const bool leader = blockIdx.x == 0;
-  if (leader && tid < cvw && chan_ok) {
+  if (leader && holder && hc0 < C) {
     float* so = const_cast<float*>(A.stats_local);  // an output here (the apply kernel only reads it)
 #pragma unroll
     for (int k = 0; k < N; ++k) {
-      so[c0 + k] = mean[k];
-      so[C + c0 + k] = m2[k];
+      so[hc0 + k] = mean[k];
+      so[C + hc0 + k] = m2[k];
     }
-    if (tid == 0 && blockIdx.y == 0) so[2 * C] = n;
+    if (wrp == 0 && blockIdx.y == 0) so[2 * C] = n;
   }
   if (P.world > 1) {
     if (leader) {
-      if (tid < cvw) {
+      if (holder) {
 #pragma unroll
         for (int k = 0; k < N; ++k) {
-          mine[cv * N + k] = mean[k];
-          mine[cw + cv * N + k] = m2[k];
+          mine[wrp * N + k] = mean[k];
+          mine[cw + wrp * N + k] = m2[k];
         }
-        if (tid == 0) mine[2 * cw] = n;
+        if (wrp == 0) mine[2 * cw] = n;
       }
       __syncthreads();
       push_chunk(P, seq, C, cb, cw, mine);
     }
     wait_and_gather(P, seq, C, cb, cw, xr);
   }
-  if (tid < cvw && chan_ok) {
+  if (holder && hc0 < C) {
     if (P.world > 1) {
       n = 0.f;
 #pragma unroll
       for (int k = 0; k < N; ++k) mean[k] = m2[k] = 0.f;
       for (int p = 0; p < P.world; ++p) {
         const float* o = xr + p * kXrStride;
-        welford_merge<N>(n, mean, m2, o[2 * cw], o + cv * N, o + cw + cv * N);
+        welford_merge<N>(n, mean, m2, o[2 * cw], o + wrp * N, o + cw + wrp * N);
       }
     }
     const float inv_n = n > 0.f ? 1.0f / n : 0.f;
@@ -1301,22 +1342,22 @@ bn_fwd_fused_kernel(const __grid_constant__ FwdArgs A, const FusedGeom G, const 
     for (int k = 0; k < N; ++k) {
       const float var = m2[k] * inv_n;
       const float invstd = 1.0f / sqrtf(var + A.eps);
-      a[k] = invstd * (A.weight ? A.weight[c0 + k] : 1.f);
-      b[k] = A.bias ? A.bias[c0 + k] : 0.f;
+      a[k] = invstd * (A.weight ? A.weight[hc0 + k] : 1.f);
+      b[k] = A.bias ? A.bias[hc0 + k] : 0.f;
       if (leader) {
-        A.save_mean[c0 + k] = mean[k];
-        A.save_invstd[c0 + k] = invstd;
+        A.save_mean[hc0 + k] = mean[k];
+        A.save_invstd[hc0 + k] = invstd;
         if (A.running_mean)
-          A.running_mean[c0 + k] = (1.f - A.momentum) * A.running_mean[c0 + k] + A.momentum * mean[k];
+          A.running_mean[hc0 + k] = (1.f - A.momentum) * A.running_mean[hc0 + k] + A.momentum * mean[k];
         if (A.running_var)
-          A.running_var[c0 + k] = (1.f - A.momentum) * A.running_var[c0 + k] + A.momentum * (m2[k] * inv_nm1);
+          A.running_var[hc0 + k] = (1.f - A.momentum) * A.running_var[hc0 + k] + A.momentum * (m2[k] * inv_nm1);
       }
       mean[k] = -mean[k];
     }
-    if (leader && tid == 0 && blockIdx.y == 0) A.save_count[0] = n;
-    sts_vec<N>(&coef[0][cv * N], mean);
-    sts_vec<N>(&coef[1][cv * N], a);
-    sts_vec<N>(&coef[2][cv * N], b);
+    if (leader && wrp == 0 && blockIdx.y == 0) A.save_count[0] = n;
+    sts_vec<N>(&coef[0][wrp * N], mean);
+    sts_vec<N>(&coef[1][wrp * N], a);
+    sts_vec<N>(&coef[2][wrp * N], b);
   }
   __syncthreads();
   float nmean[N], a[N], b[N];
@@ -1372,20 +1413,22 @@ struct BwdFusedArgs {
 };
 
 template <typename T, int RELU, bool DRES>
-__global__ void __launch_bounds__(kT, kOccBwd)
+__global__ void __launch_bounds__(kBwdThreads, 1)
 bn_bwd_fused_kernel(const __grid_constant__ BwdFusedArgs F, const FusedGeom G,
                     const __grid_constant__ b200dp_peers P, uint32_t seq) {
   constexpr int N = Vec<T>::N;
   constexpr int W = 2 * N + 1;
-  using Ring1 = RowRing<RELU >= 2 ? 3 : 4, RELU >= 2 ? 3 : 2, false, RELU == 3>;
-  using Ring2 = RowRing<RELU >= 2 ? 3 : 4, RELU >= 2 ? 3 : 2, true, RELU == 3>;
-  __shared__ __align__(16) unsigned char smem[Ring1::kBytes];
+  constexpr int NT = kBwdThreads;
+  using Ring1 = RowRing<RELU >= 2 ? 3 : 4, RELU >= 2 ? 3 : 2, false, RELU == 3, NT>;
+  using Ring2 = RowRing<RELU >= 2 ? 3 : 4, RELU >= 2 ? 3 : 2, true, RELU == 3, NT>;
+  unsigned char* smem = fused_dyn_smem;  // Ring1::kBytes
   __shared__ __align__(16) float xchg[kFusedMaxGroups * W];
   __shared__ __align__(16) float mine[2 * kChunkMax + 8];
   __shared__ __align__(16) float coef[2][kChunkMax];
+  __shared__ __align__(16) float xr[B200DP_MAX_WORLD * kXrStride];
   const BwdArgs& A = F.b;
-  const int tid = threadIdx.x;
-  const int cvw = G.cvw, cs = G.cs, rp = kT / cvw;
+  const int tid = threadIdx.x, lane = tid & 31, wrp = tid >> 5;
+  const int cvw = G.cvw, cs = G.cs, rp = NT / cvw;
   const int cv = tid % cvw, r = tid / cvw;
   const int C = A.C;
   const int cw = cvw * N, cb = blockIdx.y * cw;
@@ -1481,8 +1524,10 @@ bn_bwd_fused_kernel(const __grid_constant__ BwdFusedArgs F, const FusedGeom G,
   }
   __syncthreads();
   float dummy = 0.f;
-  cta_fold<N, false>(cvw, reinterpret_cast<float*>(smem), dummy, s1, s2);
+  cta_fold_big<N, false>(cvw, reinterpret_cast<float*>(smem), dummy, s1, s2);
   cluster_fold<N, false>(cvw, cs, mine, xchg, dummy, s1, s2, std::move(started));
+  const bool holder = lane == 0 && wrp < cvw;
+  const int hc0 = cb + wrp * N;
 
   const bool rev = G.rev2 != 0;
   const int64_t off2 = off_first + (rev ? (int64_t)(rr.count - 1) * rstep : 0);
@@ -1500,32 +1545,31 @@ bn_bwd_fused_kernel(const __grid_constant__ BwdFusedArgs F, const FusedGeom G,
   ring2.prime(nrows, ptrs2);
 
   const bool leader = blockIdx.x == 0;
-  if (leader && tid < cvw && chan_ok) {
+  if (leader && holder && hc0 < C) {
 #pragma unroll
     for (int k = 0; k < N; ++k) {
-      F.sums_local[c0 + k] = s1[k];
-      F.sums_local[C + c0 + k] = s2[k];
-      if (F.grad_bias) F.grad_bias[c0 + k] = s1[k];
-      if (F.grad_weight) F.grad_weight[c0 + k] = s2[k] * A.save_invstd[c0 + k];
+      F.sums_local[hc0 + k] = s1[k];
+      F.sums_local[C + hc0 + k] = s2[k];
+      if (F.grad_bias) F.grad_bias[hc0 + k] = s1[k];
+      if (F.grad_weight) F.grad_weight[hc0 + k] = s2[k] * A.save_invstd[hc0 + k];
     }
   }
-  __shared__ __align__(16) float xr[B200DP_MAX_WORLD * kXrStride];
   if (P.world > 1) {
     if (leader) {
-      if (tid < cvw) {
+      if (holder) {
 #pragma unroll
         for (int k = 0; k < N; ++k) {
-          mine[cv * N + k] = s1[k];
-          mine[cw + cv * N + k] = s2[k];
+          mine[wrp * N + k] = s1[k];
+          mine[cw + wrp * N + k] = s2[k];
         }
-        if (tid == 0) mine[2 * cw] = 0.f;
+        if (wrp == 0) mine[2 * cw] = 0.f;
       }
       __syncthreads();
       push_chunk(P, seq, C, cb, cw, mine);
     }
     wait_and_gather(P, seq, C, cb, cw, xr);
   }
-  if (tid < cvw && chan_ok) {
+  if (holder && hc0 < C) {
     if (P.world > 1) {
 #pragma unroll
       for (int k = 0; k < N; ++k) s1[k] = s2[k] = 0.f;
@@ -1533,8 +1577,8 @@ bn_bwd_fused_kernel(const __grid_constant__ BwdFusedArgs F, const FusedGeom G,
         const float* o = xr + p * kXrStride;
 #pragma unroll
         for (int k = 0; k < N; ++k) {
-          s1[k] += o[cv * N + k];
-          s2[k] += o[cw + cv * N + k];
+          s1[k] += o[wrp * N + k];
+          s2[k] += o[cw + wrp * N + k];
         }
       }
     }
@@ -1543,12 +1587,12 @@ bn_bwd_fused_kernel(const __grid_constant__ BwdFusedArgs F, const FusedGeom G,
     float nmdy[N], nkx[N];
 #pragma unroll
     for (int k = 0; k < N; ++k) {
-      const float invstd = A.save_invstd[c0 + k];
+      const float invstd = A.save_invstd[hc0 + k];
       nmdy[k] = -(s1[k] * inv_cnt);
       nkx[k] = -(s2[k] * inv_cnt * invstd * invstd);
     }
-    sts_vec<N>(&coef[0][cv * N], nmdy);
-    sts_vec<N>(&coef[1][cv * N], nkx);
+    sts_vec<N>(&coef[0][wrp * N], nmdy);
+    sts_vec<N>(&coef[1][wrp * N], nkx);
   }
   __syncthreads();
   float nmdy[N], nkx[N];
@@ -1652,6 +1696,7 @@ struct FusedCfg {
   bool on;
   int64_t fwd_bytes, bwd_bytes;
   int cs;
+  bool any_geometry;  // take every shape under the size limits, whatever geometry fits (tests, measurements)
 };
 FusedCfg& fused_cfg() {  // read from the environment once; b200dp_bn_set_one_kernel_limits() may change it later
   static FusedCfg cfg = [] {
@@ -1661,9 +1706,11 @@ FusedCfg& fused_cfg() {  // read from the environment once; b200dp_bn_set_one_ke
     e = getenv("B200DP_BN_FUSED_MB");
     c.fwd_bytes = (int64_t)(e && e[0] ? atoi(e) : 56) << 20;
     e = getenv("B200DP_BN_FUSED_BWD_MB");
-    c.bwd_bytes = (int64_t)(e && e[0] ? atoi(e) : 40) << 20;
+    c.bwd_bytes = (int64_t)(e && e[0] ? atoi(e) : 56) << 20;
     e = getenv("B200DP_BN_FUSED_CS");
-    c.cs = (e && atoi(e) == 8) ? 8 : kFusedMaxCS;
+    c.cs = (e && atoi(e) >= 1 && atoi(e) <= kFusedMaxCS) ? atoi(e) : kFusedMaxCS;
+    e = getenv("B200DP_BN_FUSED_ANY");
+    c.any_geometry = e && e[0] == '1';
     return c;
   }();
   return cfg;
@@ -1675,38 +1722,54 @@ struct FusedPlan {
   int chunks;
 };
 
-// Candidates (vectors per row chunk, cluster size): wide chunks use whole 128-byte lines, narrow ones
-// give more clusters.  Take the widest that still yields >= 256 CTAs, else the one with the most CTAs.
+// Geometry of the one-kernel path, and whether it is worth taking.  Measured on B200 (profiles/
+// r2_bn_warm8_*.txt, back-to-back launches): it beats the two kernels only where a chunk is a whole
+// 128-byte line (narrower chunks cost one L1 wavefront per 32 or 64 bytes and lose more than the second
+// launch costs), the clusters fill most of the SMs, and the clusters are small or the tensor is tiny
+// (16-CTA clusters pay more at the cluster barrier than a ~5 us launch).  That is: C >= 1024 bf16
+// channels (cluster size <= 4 ... 8) or tensors up to 16 MiB.  With `any_geometry` (tests, measurements)
+// every shape under the size limit goes through it, with whatever geometry fits.
 template <typename T, typename KernelT>
-FusedPlan plan_fused(KernelT kernel, int64_t M, int C, int64_t limit_bytes) {
+FusedPlan plan_fused(KernelT kernel, int threads, int dyn_smem, int64_t M, int C, int64_t limit_bytes) {
   FusedPlan pl;
   pl.ok = false;
   const FusedCfg& cfg = fused_cfg();
-  if (!cfg.on || limit_bytes <= 0 || M * C * (int64_t)sizeof(T) > limit_bytes) return pl;
-  const int big = (cfg.cs == kFusedMaxCS && max_active_clusters(kernel, kFusedMaxCS) > 0) ? kFusedMaxCS : 8;
+  const int64_t bytes = M * C * (int64_t)sizeof(T);
+  if (!cfg.on || limit_bytes <= 0 || bytes > limit_bytes) return pl;
+  const bool forced = cfg.any_geometry;
   const int nvec = C / Vec<T>::N;
-  const int cand[3][2] = {{8, 8}, {4, big}, {2, big}};
-  int best = -1, best_ctas = 0;
-  for (int i = 0; i < 3; ++i) {
-    const int chunks = (nvec + cand[i][0] - 1) / cand[i][0];
-    const int ctas = chunks * cand[i][1];
-    if (ctas >= 256) { best = i; break; }
-    if (ctas > best_ctas) { best = i; best_ctas = ctas; }
+  int best_ctas = 0;
+  for (int cvw = 8; cvw >= 2; cvw >>= 1) {
+    const int chunks = (nvec + cvw - 1) / cvw;
+    int cs = 0;
+    for (int c = kFusedMaxCS; c >= 1; c >>= 1) {
+      if (c > cfg.cs) continue;
+      if (max_active_clusters(kernel, c, threads, dyn_smem) >= chunks) { cs = c; break; }
+    }
+    if (cs == 0) continue;  // more chunks than SMs even with single-CTA clusters: try a wider chunk (none: two kernels)
+    const int ctas = chunks * cs;
+    if (ctas > best_ctas) {
+      best_ctas = ctas;
+      pl.g.cvw = cvw;
+      pl.g.cs = cs;
+      pl.chunks = chunks;
+    }
+    if (ctas >= 96 || !forced) break;  // unforced: whole lines (cvw = 8) or nothing
   }
-  pl.g.cvw = cand[best][0];
-  pl.g.cs = cand[best][1];
+  if (best_ctas == 0) return pl;
+  if (!forced && (best_ctas < 96 || (pl.g.cs > 4 && bytes > ((int64_t)16 << 20)))) return pl;
   pl.g.rev2 = 1;
-  pl.chunks = (nvec + pl.g.cvw - 1) / pl.g.cvw;
   pl.ok = true;
   return pl;
 }
 
 template <typename... KArgs, typename... Args>
-cudaError_t launch_cluster(void (*kernel)(KArgs...), int cs, int chunks, cudaStream_t s, bool pdl, Args... args) {
+cudaError_t launch_cluster(void (*kernel)(KArgs...), int cs, int chunks, int threads, int dyn_smem, cudaStream_t s,
+                           bool pdl, Args... args) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(cs, chunks, 1);
-  cfg.blockDim = dim3(kT, 1, 1);
-  cfg.dynamicSmemBytes = 0;
+  cfg.blockDim = dim3(threads, 1, 1);
+  cfg.dynamicSmemBytes = dyn_smem;
   cfg.stream = s;
   cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -1728,9 +1791,10 @@ int launch_fwd_fused(const FwdArgs& A, bool relu, const b200dp_peers& P, uint32_
   cudaError_t e;
 #define B200DP_FWD_FUSED(RELU, RES)                                                              \
   do {                                                                                           \
-    const FusedPlan pl = plan_fused<T>(bn_fwd_fused_kernel<T, RELU, RES>, A.M, A.C, fused_cfg().fwd_bytes); \
+    constexpr int smem = 8 * kFwdThreads * 16; /* the deeper of the two rings */                 \
+    const FusedPlan pl = plan_fused<T>(bn_fwd_fused_kernel<T, RELU, RES>, kFwdThreads, smem, A.M, A.C, fused_cfg().fwd_bytes); \
     if (!pl.ok) return kNotFused;                                                                \
-    e = launch_cluster(bn_fwd_fused_kernel<T, RELU, RES>, pl.g.cs, pl.chunks, s, pdl_first(), A, pl.g, P, seq); \
+    e = launch_cluster(bn_fwd_fused_kernel<T, RELU, RES>, pl.g.cs, pl.chunks, kFwdThreads, smem, s, pdl_first(), A, pl.g, P, seq); \
   } while (0)
   if (relu && res) B200DP_FWD_FUSED(true, true);
   else if (relu) B200DP_FWD_FUSED(true, false);
@@ -1748,9 +1812,10 @@ int launch_bwd_fused(const BwdFusedArgs& F, int relu, const b200dp_peers& P, uin
   cudaError_t e = cudaSuccess;
 #define B200DP_BWD_FUSED(R, D)                                                                   \
   do {                                                                                           \
-    const FusedPlan pl = plan_fused<T>(bn_bwd_fused_kernel<T, R, D>, F.b.M, F.b.C, fused_cfg().bwd_bytes); \
+    constexpr int smem = (R >= 2 ? 9 : 8) * kBwdThreads * 16;                                    \
+    const FusedPlan pl = plan_fused<T>(bn_bwd_fused_kernel<T, R, D>, kBwdThreads, smem, F.b.M, F.b.C, fused_cfg().bwd_bytes); \
     if (!pl.ok) return kNotFused;                                                                \
-    e = launch_cluster(bn_bwd_fused_kernel<T, R, D>, pl.g.cs, pl.chunks, s, pdl_first(), F, pl.g, P, seq); \
+    e = launch_cluster(bn_bwd_fused_kernel<T, R, D>, pl.g.cs, pl.chunks, kBwdThreads, smem, s, pdl_first(), F, pl.g, P, seq); \
   } while (0)
 #define B200DP_BWD_FUSED_R(R)            \
   do {                                   \
@@ -2133,20 +2198,28 @@ extern "C" int b200dp_bn_backward(const void* dy, const void* x, const void* y_o
 // the apply kernel.  For callers that time or count launches; the results are the same either way.
 // Limits of the one-kernel path at run time (tests and A/B measurements; not thread-safe against calls in
 // flight on other host threads): tensor size bounds in MiB for the forward / backward (0 = never, < 0 =
-// leave as it is) and the cluster size (8 or 16, anything else = leave as it is).
-extern "C" int b200dp_bn_set_one_kernel_limits(int fwd_mb, int bwd_mb, int cluster_size) {
+// leave as it is), the largest cluster size (1..16, anything else = leave as it is), and whether every shape
+// under the limits takes the path whatever geometry fits (1) or only the shapes it was measured to win on
+// (0, the default; < 0 = leave as it is).
+extern "C" int b200dp_bn_set_one_kernel_limits(int fwd_mb, int bwd_mb, int cluster_size, int any_geometry) {
   FusedCfg& cfg = fused_cfg();
+  if (any_geometry >= 0) cfg.any_geometry = any_geometry != 0;
   if (fwd_mb >= 0) cfg.fwd_bytes = (int64_t)fwd_mb << 20;
   if (bwd_mb >= 0) cfg.bwd_bytes = (int64_t)bwd_mb << 20;
-  if (cluster_size == 8 || cluster_size == kFusedMaxCS) cfg.cs = cluster_size;
+  if (cluster_size >= 1 && cluster_size <= kFusedMaxCS) cfg.cs = cluster_size;  // an upper bound: powers of two up to it are tried
   cfg.on = cfg.fwd_bytes > 0 || cfg.bwd_bytes > 0;
   return B200DP_OK;
 }
 
 extern "C" int b200dp_bn_one_kernel(int dtype, int64_t M, int C, int backward) {
   const FusedCfg& cfg = fused_cfg();
-  if (!cfg.on || (dtype != B200DP_F32 && dtype != B200DP_BF16)) return 0;
-  const int64_t bytes = M * C * (dtype == B200DP_BF16 ? 2 : 4);
-  const int64_t limit = backward ? cfg.bwd_bytes : cfg.fwd_bytes;
-  return (limit > 0 && bytes <= limit) ? 1 : 0;
+  if (!cfg.on || (dtype != B200DP_F32 && dtype != B200DP_BF16) || C <= 0 || M < 0) return 0;
+  // the planner's answer does not depend on the epilogue variant: ask with the plain one
+  if (dtype == B200DP_BF16) {
+    if (backward)
+      return plan_fused<__nv_bfloat16>(bn_bwd_fused_kernel<__nv_bfloat16, 0, false>, kBwdThreads, 8 * kBwdThreads * 16, M, C, cfg.bwd_bytes).ok;
+    return plan_fused<__nv_bfloat16>(bn_fwd_fused_kernel<__nv_bfloat16, false, false>, kFwdThreads, 8 * kFwdThreads * 16, M, C, cfg.fwd_bytes).ok;
+  }
+  if (backward) return plan_fused<float>(bn_bwd_fused_kernel<float, 0, false>, kBwdThreads, 8 * kBwdThreads * 16, M, C, cfg.bwd_bytes).ok;
+  return plan_fused<float>(bn_fwd_fused_kernel<float, false, false>, kFwdThreads, 8 * kFwdThreads * 16, M, C, cfg.fwd_bytes).ok;
 }

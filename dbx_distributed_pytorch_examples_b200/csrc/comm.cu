@@ -109,12 +109,49 @@ extern "C" int b200dp_comm_create(int rank, int world, size_t heap_bytes, b200dp
   return B200DP_OK;
 }
 
+// A communicator over a heap the CALLER allocated and mapped on every rank (e.g. torch's symmetric
+// memory: cuMemCreate + fd exchange + cuMulticastBindMem), so that the bucket kernel can use the
+// switch's multicast address.  Only the small flag / exchange area is still allocated and IPC-exported
+// here.  heap_ptrs[r] = rank r's heap as mapped in THIS process; heap_multicast may be NULL.
+extern "C" int b200dp_comm_create_external(int rank, int world, size_t heap_bytes, void* const* heap_ptrs,
+                                           void* heap_multicast, b200dp_comm** out) {
+  if (!out || !heap_ptrs || world < 1 || world > B200DP_MAX_WORLD || rank < 0 || rank >= world) return B200DP_EINVAL;
+  for (int r = 0; r < world; ++r)
+    if (!heap_ptrs[r] || ((uintptr_t)heap_ptrs[r] & 15)) return B200DP_EALIGN;
+  if ((uintptr_t)heap_multicast & 15) return B200DP_EALIGN;
+  b200dp_comm* c = new (std::nothrow) b200dp_comm();
+  if (!c) return (int)cudaErrorMemoryAllocation;
+  memset(c, 0, sizeof(*c));
+  c->rank = rank;
+  c->world = world;
+  c->heap_bytes = heap_bytes;
+  c->heap_external = true;
+  c->heap_mc = heap_multicast;
+  cudaError_t e = cudaGetDevice(&c->device);
+  void* sync = nullptr;
+  if (e == cudaSuccess) e = cudaMalloc(&sync, sizeof(b200dp_sync_area));
+  if (e == cudaSuccess) e = cudaMemset(sync, 0, sizeof(b200dp_sync_area));
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) {
+    if (sync) cudaFree(sync);
+    delete c;
+    return (int)e;
+  }
+  for (int r = 0; r < world; ++r) c->heap[r] = heap_ptrs[r];
+  c->sync[rank] = static_cast<b200dp_sync_area*>(sync);
+  c->peers_open = (world == 1);
+  *out = c;
+  return B200DP_OK;
+}
+
+extern "C" int b200dp_comm_has_multicast(const b200dp_comm* comm) { return comm && comm->heap_mc ? 1 : 0; }
+
 extern "C" int b200dp_comm_export(b200dp_comm* comm, void* out) {
   if (!comm || !out) return B200DP_EINVAL;
   ExportBlob blob;
   memset(&blob, 0, sizeof(blob));
   if (comm->world > 1) {
-    B200DP_CUDA_TRY(cudaIpcGetMemHandle(&blob.heap, comm->heap[comm->rank]));
+    if (!comm->heap_external) B200DP_CUDA_TRY(cudaIpcGetMemHandle(&blob.heap, comm->heap[comm->rank]));
     B200DP_CUDA_TRY(cudaIpcGetMemHandle(&blob.sync, comm->sync[comm->rank]));
   }
   memcpy(out, &blob, sizeof(blob));
@@ -129,9 +166,11 @@ extern "C" int b200dp_comm_open_peers(b200dp_comm* comm, const void* all_handles
     if (p == comm->rank) continue;
     void* heap = nullptr;
     void* sync = nullptr;
-    B200DP_CUDA_TRY(cudaIpcOpenMemHandle(&heap, blobs[p].heap, cudaIpcMemLazyEnablePeerAccess));
+    if (!comm->heap_external) {
+      B200DP_CUDA_TRY(cudaIpcOpenMemHandle(&heap, blobs[p].heap, cudaIpcMemLazyEnablePeerAccess));
+      comm->heap[p] = heap;
+    }
     B200DP_CUDA_TRY(cudaIpcOpenMemHandle(&sync, blobs[p].sync, cudaIpcMemLazyEnablePeerAccess));
-    comm->heap[p] = heap;
     comm->sync[p] = static_cast<b200dp_sync_area*>(sync);
   }
   comm->peers_open = true;
@@ -143,10 +182,10 @@ extern "C" int b200dp_comm_destroy(b200dp_comm* comm) {
   cudaDeviceSynchronize();
   for (int p = 0; p < comm->world; ++p) {
     if (p == comm->rank) continue;
-    if (comm->heap[p]) cudaIpcCloseMemHandle(comm->heap[p]);
+    if (comm->heap[p] && !comm->heap_external) cudaIpcCloseMemHandle(comm->heap[p]);
     if (comm->sync[p]) cudaIpcCloseMemHandle(comm->sync[p]);
   }
-  if (comm->heap[comm->rank]) cudaFree(comm->heap[comm->rank]);
+  if (comm->heap[comm->rank] && !comm->heap_external) cudaFree(comm->heap[comm->rank]);
   if (comm->sync[comm->rank]) cudaFree(comm->sync[comm->rank]);
   delete comm;
   return B200DP_OK;

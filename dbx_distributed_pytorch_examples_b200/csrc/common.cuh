@@ -255,6 +255,10 @@ struct b200dp_comm {
   b200dp_sync_area* sync[B200DP_MAX_WORLD];   // sync[rank] is the local one
   bool peers_open;
   uint32_t seq;
+  // b200dp_comm_create_external: the heap belongs to the caller (all ranks' mappings handed in), and
+  // heap_mc, when not NULL, is a multicast (NVLS) mapping of the same memory on all ranks
+  bool heap_external;
+  void* heap_mc;
 };
 
 // Passed by value to kernels (as a __grid_constant__ parameter wherever sync[] is indexed at run time,

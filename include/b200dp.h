@@ -269,8 +269,9 @@ int b200dp_bn_backward(const void* dy, const void* x, const void* y_out, void* d
                        uint32_t seq, b200dp_stream_t stream);
 
 /* 1 when b200dp_bn_forward (backward != 0: b200dp_bn_backward) runs a layer of this shape as ONE
- * kernel, 0 when it issues two.  Layers whose tensor fits the L2 (B200DP_BN_FUSED_MB /
- * B200DP_BN_FUSED_BWD_MB MiB, environment; B200DP_BN_FUSED=0 turns the path off) are handled by one
+ * kernel, 0 when it issues two.  Small layers (tensor within B200DP_BN_FUSED_MB / B200DP_BN_FUSED_BWD_MB
+ * MiB — default 56: what stays in the 126 MB L2 — and a shape the path was measured to win on, see
+ * below; B200DP_BN_FUSED=0 turns the path off) are handled by one
  * thread-block cluster per channel chunk: rows streamed once for the statistics (sums), folded over the
  * cluster through distributed shared memory, exchanged across ranks, and streamed again out of the L2
  * for the normalise (dx) pass.  Same arguments, same results, same exchange words as the two-kernel
@@ -278,9 +279,13 @@ int b200dp_bn_backward(const void* dy, const void* x, const void* y_out, void* d
  * For callers that time or count launches. */
 int b200dp_bn_one_kernel(int dtype, int64_t M, int C, int backward);
 /* The same limits at run time (tests, A/B measurements): MiB bounds for the forward / backward
- * (0 = never take the one-kernel path, < 0 = leave unchanged) and the cluster size (8 or 16; anything
- * else = leave unchanged).  Not synchronised with calls in flight on other host threads. */
-int b200dp_bn_set_one_kernel_limits(int fwd_mb, int bwd_mb, int cluster_size);
+ * (0 = never take the one-kernel path, < 0 = leave unchanged), the largest cluster size (1..16;
+ * anything else = leave unchanged), and any_geometry: 1 = every shape under the bounds takes the path
+ * with whatever geometry fits, 0 = only the shapes it was measured to win on (rows of >= 2 KB, i.e.
+ * C >= 1024 bf16 channels, or tensors up to 16 MiB; the default), < 0 = leave unchanged.
+ * Environment equivalents: B200DP_BN_FUSED_MB, B200DP_BN_FUSED_BWD_MB, B200DP_BN_FUSED_CS,
+ * B200DP_BN_FUSED_ANY.  Not synchronised with calls in flight on other host threads. */
+int b200dp_bn_set_one_kernel_limits(int fwd_mb, int bwd_mb, int cluster_size, int any_geometry);
 
 /* ------------------------------------------------------------------------
  * Communicator: library-owned symmetric buffers mapped into every rank.
@@ -299,6 +304,19 @@ int b200dp_bn_set_one_kernel_limits(int fwd_mb, int bwd_mb, int cluster_size);
 /* Allocates on the CURRENT device.  world==1 is valid (no peers to open). */
 int b200dp_comm_create(int rank, int world, size_t heap_bytes,
                        b200dp_comm** out);
+/* The same over a heap the CALLER owns and has mapped on every rank: heap_ptrs[r] (HOST array of `world`
+ * device pointers, 16-byte aligned) is rank r's heap as seen from this process, heap_multicast (may be
+ * NULL) a multicast mapping of the same bytes on all ranks (NVLink SHARP / NVLS: cuMulticastCreate +
+ * cuMulticastBindMem, which torch.distributed._symmetric_memory does for its allocations).  With a
+ * multicast mapping the two-shot bucket kernel reduces in the switch (multimem.ld_reduce) and pushes the
+ * new parameters with one multicast store instead of one store per peer.  Only the flag / exchange area
+ * is allocated (and exported / opened through the two calls below) by the library; the heap is never
+ * freed by b200dp_comm_destroy. */
+int b200dp_comm_create_external(int rank, int world, size_t heap_bytes,
+                                void* const* heap_ptrs, void* heap_multicast,
+                                b200dp_comm** out);
+/* 1 when the communicator's heap has a multicast mapping. */
+int b200dp_comm_has_multicast(const b200dp_comm* comm);
 /* Copies this rank's B200DP_COMM_HANDLE_BYTES export blob to `out` (host). */
 int b200dp_comm_export(b200dp_comm* comm, void* out);
 /* all_handles: host, world * B200DP_COMM_HANDLE_BYTES, indexed by rank. */

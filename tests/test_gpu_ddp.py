@@ -128,10 +128,11 @@ def _grad_errors_against_float64(x, y, build_ours):
     relative L2 distance to the float64 gradient of that tensor."""
     ref, m = make_pair()
     arb = copy.deepcopy(ref).double()
+    x = x.contiguous(memory_format=torch.channels_last)   # the same layout (hence the same cuDNN algorithms) for all three
     F.cross_entropy(arb(x.double()), y).backward()
     F.cross_entropy(ref(x), y).backward()
     ours = build_ours(m)
-    F.cross_entropy(ours(x.contiguous(memory_format=torch.channels_last)), y).backward()
+    F.cross_entropy(ours(x), y).backward()
     out = {}
     for (n, a), t, o in zip(arb.named_parameters(), ref.parameters(), m.parameters()):
         g = a.grad
@@ -158,11 +159,14 @@ def test_per_tensor_grads_against_float64_arbiter():
 
 
 def test_plain_bn_model_grads_against_float64_arbiter():
-    """The same measurement without our BatchNorm (wrapper only): the pack + reduce path adds nothing."""
+    """The same measurement without our BatchNorm (wrapper only: torch's own kernels on both sides, so the
+    pack + reduce path must add nothing).  It also shows the scale every float32-vs-float32 comparison of this
+    network has to be read against: float32 itself is up to ~1e-2 away from float64 on the early BN weights."""
     x, y = batch(1, 64)
     errs = _grad_errors_against_float64(x, y, lambda m: b200.B200DDP(m, device_ids=[0]))
     for n, (eo, et) in errs.items():
-        assert eo <= 1.2 * et + 1e-7, (n, eo, et)
+        assert eo <= 1.05 * et + 1e-7, (n, eo, et)
+    assert max(et for _, et in errs.values()) > 1e-4   # float32 vs float64 on this network is NOT a 1e-5 affair
 
 
 def test_comm_hook_compat():
@@ -370,7 +374,7 @@ def test_checkpoint_resume_through_the_fused_optimizer(opt):
     m_c = workloads.cifar_resnet18(10).cuda()
     ddp_c = b200.B200DDP(m_c, device_ids=[0]); o_c = ddp_c.fuse_optimizer(mk(ddp_c.parameters()))
     ddp_c.module.load_state_dict(ck["model"]); o_c.load_state_dict(ck["optimizer"])
-    assert ddp_c._opt_step_count == 3
+    assert ddp_c._opt_step_count == (3 if opt == "adam" else 1)   # SGD only needs to know the first step is behind it
     run(ddp_c, o_c, range(3, 6))
     for (n, a), c in zip(m_a.named_parameters(), m_c.parameters()):
         torch.testing.assert_close(c, a, rtol=1e-5, atol=1e-6, msg=lambda s: f"{n}: {s}")

@@ -76,7 +76,7 @@ def _w_syncbn():
     # with the larger batches on the two-kernel path and the others on the one-kernel path in the SAME exchange.
     lib = _lib.lib()
     worst = {}
-    for limits in ((0, 0, -1), (1 << 20, 1 << 20, 16), (1, 1, 8)):
+    for limits in ((0, 0, -1, 0), (1 << 20, 1 << 20, 16, 1), (1, 1, 8, 1)):
         lib.b200dp_bn_set_one_kernel_limits(*limits)
         for dtype, tol in ((torch.float32, dict(rtol=1e-4, atol=1e-5)), (torch.bfloat16, dict(rtol=2e-2, atol=2e-2))):
             torch.manual_seed(10 + rank)
@@ -105,7 +105,7 @@ def _w_syncbn():
                 if n:
                     key = ("y", str(dtype)); worst[key] = max(worst.get(key, 0.0), float((ya.float() - yb.float()).abs().max()))
                     key = ("dx", str(dtype)); worst[key] = max(worst.get(key, 0.0), float((xa.grad.float() - xb.grad.float()).abs().max()))
-    lib.b200dp_bn_set_one_kernel_limits(56, 40, 16)
+    lib.b200dp_bn_set_one_kernel_limits(56, 56, 16, 0)
     from dbx_distributed_pytorch_examples_b200.comm import stats_communicator
     stats_communicator().check_error()
     dist.barrier()

@@ -75,7 +75,7 @@ def test_stem_size_properties_and_fusion():
         b200.B200MaxPool2d(5, 2, 2)
 
 
-def test_argument_errors_and_fallbacks():
+def test_argument_errors():
     lib = _lib.lib()
     x = torch.zeros((1, 8, 8, 8), device="cuda")
     y = torch.zeros((1, 4, 4, 8), device="cuda")
@@ -88,9 +88,11 @@ def test_argument_errors_and_fallbacks():
     assert f(None, y.data_ptr(), i.data_ptr(), 0, 1, 8, 8, 8, 3, 2, 1, None) == -1
     assert f(x.data_ptr() + 4, y.data_ptr(), i.data_ptr(), 0, 1, 8, 8, 8, 3, 2, 1, None) == -3
     assert f(x.data_ptr(), y.data_ptr(), i.data_ptr(), 0, 0, 8, 8, 8, 3, 2, 1, None) == 0    # empty batch
-    # channel counts the kernel does not take stay on torch's op, NaN propagates like torch's
+    # channel counts the kernel does not take are refused (no second implementation behind the module)
     odd = torch.randn(2, 3, 8, 8, device="cuda")
-    assert torch.equal(b200.B200MaxPool2d(3, 2, 1)(odd), F.max_pool2d(odd, 3, 2, 1))
+    with pytest.raises(ValueError, match="Keep nn.MaxPool2d"):
+        b200.B200MaxPool2d(3, 2, 1)(odd)
+    # NaN propagates like torch's
     z = torch.randn(1, 8, 6, 6, device="cuda").contiguous(memory_format=torch.channels_last)
     z[0, 0, 2, 2] = float("nan")
     a, b = b200.B200MaxPool2d(3, 2, 1)(z), F.max_pool2d(z, 3, 2, 1)

@@ -21,11 +21,11 @@ def bn_path(request):
     from dbx_distributed_pytorch_examples_b200 import _lib
     lib = _lib.lib()
     if request.param == "two_kernels":
-        lib.b200dp_bn_set_one_kernel_limits(0, 0, -1)
+        lib.b200dp_bn_set_one_kernel_limits(0, 0, -1, -1)
     else:
-        lib.b200dp_bn_set_one_kernel_limits(1 << 20, 1 << 20, 16 if request.param.endswith("16") else 8)
+        lib.b200dp_bn_set_one_kernel_limits(1 << 20, 1 << 20, 16 if request.param.endswith("16") else 8, 1)
     yield request.param
-    lib.b200dp_bn_set_one_kernel_limits(56, 40, 16)
+    lib.b200dp_bn_set_one_kernel_limits(56, 56, 16, 0)
 
 
 def rows(t):

@@ -36,14 +36,18 @@ def main():
                     help="backward of residual layers: 2 = ReLU mask from y (the default in training), 3 = from mask words")
     ap.add_argument("--one-kernel-mb", type=int, nargs=2, default=None, metavar=("FWD", "BWD"),
                     help="size limits of the one-kernel path for the '(1 call)' columns (0 0 = always two kernels)")
-    ap.add_argument("--cluster", type=int, default=-1, help="cluster size of the one-kernel path (8 or 16)")
+    ap.add_argument("--cluster", type=int, default=-1, help="largest cluster size of the one-kernel path (1..16)")
+    ap.add_argument("--any-geometry", type=int, default=-1, help="1: every shape under the limits takes the one-kernel path")
+    ap.add_argument("--chain", type=int, default=1,
+                    help="time this many back-to-back calls per sample (amortises the ~5 us an idle stream adds to one launch; "
+                         "closer to what a kernel costs inside a training step)")
     a = ap.parse_args()
     peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(
         os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
     lib = _lib.lib()
-    if a.one_kernel_mb is not None or a.cluster > 0:
+    if a.one_kernel_mb is not None or a.cluster > 0 or a.any_geometry >= 0:
         f, b_ = a.one_kernel_mb if a.one_kernel_mb is not None else (-1, -1)
-        lib.b200dp_bn_set_one_kernel_limits(f, b_, a.cluster)
+        lib.b200dp_bn_set_one_kernel_limits(f, b_, a.cluster, a.any_geometry)
     print(f"# one-kernel limits: {a.one_kernel_mb} cluster {a.cluster} mask mode {a.mask_mode} {'warm' if a.warm else 'cold'}")
     dt = torch.bfloat16 if a.dtype == "bf16" else torch.float32
     code, es = _lib.dtype_code(dt), (2 if dt == torch.bfloat16 else 4)
@@ -97,10 +101,11 @@ def main():
                     flush.fill_(1)
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record()
-                fn()
+                for _ in range(a.chain):
+                    fn()
                 e1.record()
                 torch.cuda.synchronize()
-                ts.append(e0.elapsed_time(e1))
+                ts.append(e0.elapsed_time(e1) / a.chain)
             ts.sort()
             ms = ts[len(ts) // 2]
             gbs = nbytes / ms / 1e6
