@@ -10,6 +10,7 @@ loads/stores issued by the kernels in csrc/.
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Optional
 
 import torch
@@ -36,7 +37,11 @@ class Communicator:
     single-rank one and nothing is exchanged.
     """
 
-    def __init__(self, process_group=None, heap_bytes: int = 0, device: Optional[torch.device] = None):
+    def __init__(self, process_group=None, heap_bytes: int = 0, device: Optional[torch.device] = None,
+                 multicast: Optional[bool] = False):
+        """``multicast``: False (default) = the heap is a cudaMalloc block shared through CUDA IPC; None = use
+        an NVLS (multicast) mapping of the heap when the platform offers one; True = require it.  With a
+        multicast mapping the two-shot bucket kernel reduces in the NVSwitch (csrc/update.cu)."""
         if dist.is_available() and dist.is_initialized():
             self.rank = dist.get_rank(process_group)
             self.world = dist.get_world_size(process_group)
@@ -48,9 +53,22 @@ class Communicator:
         self.process_group = process_group
         lib = _lib.lib()
         self._handle = ctypes.c_void_p()
+        self._symm = None
         with torch.cuda.device(self.device):
-            _lib.check(lib.b200dp_comm_create(self.rank, self.world, int(heap_bytes), ctypes.byref(self._handle)),
-                       "b200dp_comm_create")
+            symm = (self._symmetric_heap(int(heap_bytes), process_group)
+                    if (multicast is not False and self.world > 1 and heap_bytes > 0) else None)
+            if symm is not None:
+                tensor, hdl, nbytes = symm
+                off = int(getattr(hdl, "offset", 0) or 0)  # the tensor's place inside the exchanged block
+                ptrs = (ctypes.c_void_p * self.world)(*[int(p) + off for p in hdl.buffer_ptrs])
+                _lib.check(lib.b200dp_comm_create_external(self.rank, self.world, nbytes, ptrs, int(hdl.multicast_ptr) + off,
+                                                           ctypes.byref(self._handle)), "b200dp_comm_create_external")
+                self._symm = (tensor, hdl)  # the allocation lives as long as the communicator
+            else:
+                if multicast is True and self.world > 1 and heap_bytes > 0:
+                    raise _lib.B200DPError("no multicast (NVLS) mapping is available for the heap on this platform")
+                _lib.check(lib.b200dp_comm_create(self.rank, self.world, int(heap_bytes), ctypes.byref(self._handle)),
+                           "b200dp_comm_create")
             if self.world > 1:
                 blob = ctypes.create_string_buffer(_lib.COMM_HANDLE_BYTES)
                 _lib.check(lib.b200dp_comm_export(self._handle, blob), "b200dp_comm_export")
@@ -60,9 +78,36 @@ class Communicator:
                 _lib.check(lib.b200dp_comm_open_peers(self._handle, allb), "b200dp_comm_open_peers")
                 # nobody may touch a peer's flags before every rank has mapped them
                 dist.barrier(group=process_group)
+        self.multicast = bool(lib.b200dp_comm_has_multicast(self._handle))
         self.heap_bytes = int(lib.b200dp_comm_heap_bytes(self._handle))
         self._heap_ptr = int(lib.b200dp_comm_heap(self._handle, self.rank))
         self._heap_u8 = torch.as_tensor(_RawCudaBuffer(self._heap_ptr, self.heap_bytes, self), device=self.device)
+
+    def _symmetric_heap(self, heap_bytes: int, process_group):
+        """The heap as a torch symmetric-memory allocation (cuMemCreate + handle exchange + multicast
+        binding done by torch.distributed._symmetric_memory), or None when that is not available here or
+        gives no multicast address — every rank takes the same decision (it is agreed on with an all-reduce)."""
+        ok, out = 1, None
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+
+            nbytes = max(1, (heap_bytes + (2 << 20) - 1) >> 21) << 21
+            group = process_group if process_group is not None else dist.group.WORLD
+            t = symm_mem.empty(nbytes, dtype=torch.uint8, device=self.device)
+            hdl = symm_mem.rendezvous(t, group)
+            off = int(getattr(hdl, "offset", 0) or 0)
+            if (not int(hdl.multicast_ptr) or len(hdl.buffer_ptrs) != self.world
+                    or int(hdl.buffer_ptrs[self.rank]) + off != t.data_ptr()):
+                ok = 0
+            else:
+                t.zero_()
+                out = (t, hdl, nbytes)
+        except Exception:  # noqa: BLE001  (no driver support, no NVSwitch, an older torch, ...)
+            ok = 0
+        flag = torch.tensor([ok], dtype=torch.int32, device=self.device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=process_group)
+        torch.cuda.synchronize(self.device)
+        return out if int(flag) == 1 else None
 
     # -- C handle ------------------------------------------------------------------
     @property
@@ -111,6 +156,7 @@ class Communicator:
             self._heap_u8 = None
             _lib.lib().b200dp_comm_destroy(self._handle)
             self._handle = ctypes.c_void_p()
+            self._symm = None
 
 
 _stats_comms = {}

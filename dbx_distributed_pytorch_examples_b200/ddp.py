@@ -30,6 +30,7 @@ from __future__ import annotations
 
 import ctypes
 import math
+import os
 from contextlib import contextmanager
 from typing import List, Optional
 
@@ -141,7 +142,7 @@ class B200DDP(DistributedDataParallel):
                  check_reduction=False, gradient_as_bucket_view=False, static_graph=False,
                  delay_all_reduce_named_params=None, param_to_hook_all_reduce=None,
                  mixed_precision=None, device_mesh=None, skip_all_reduce_unused_params=False, *,
-                 one_shot_bytes: int = 256 * 1024, max_ctas: int = 48):
+                 one_shot_bytes: int = 256 * 1024, max_ctas: int = 48, nvls=None):
         torch.nn.Module.__init__(self)
         if mixed_precision is not None or device_mesh is not None or delay_all_reduce_named_params is not None:
             raise NotImplementedError("B200DDP does not implement mixed_precision / device_mesh / delayed all-reduce")
@@ -201,7 +202,13 @@ class B200DDP(DistributedDataParallel):
             a.grad_off, a.param_off = heap, heap + nbytes
             heap += 2 * nbytes
         with torch.cuda.device(self.device):
-            self.comm = Communicator(process_group, heap_bytes=heap, device=self.device)
+            # nvls: True = the heap must have a multicast (NVLS) mapping, "auto" = use one when the platform
+            # offers it, False = plain IPC heap and the peer load/store kernel; None = what B200DP_NVLS says
+            # in the environment ("1", "auto", anything else or unset = off)
+            if nvls is None:
+                nvls = {"1": True, "auto": "auto"}.get(os.environ.get("B200DP_NVLS", "0"), False)
+            multicast = None if nvls == "auto" else bool(nvls)
+            self.comm = Communicator(process_group, heap_bytes=heap, device=self.device, multicast=multicast)
             self._comm_stream = torch.cuda.Stream(device=self.device)
         self._param_index = {}
         self._buckets: List[_BucketState] = []

@@ -126,10 +126,16 @@ def _w_allreduce():
     worst = {}
     for dtype, tol in ((torch.float32, dict(rtol=1e-5, atol=1e-6)), (torch.bfloat16, dict(rtol=2e-2, atol=2e-2))):
         code, es = _lib.dtype_code(dtype), (2 if dtype == torch.bfloat16 else 4)
-        for kind in ("sgd", "adam"):
+        # heap: a cudaMalloc block shared through CUDA IPC (peer load/store kernel), and — where the platform
+        # has NVLS — a symmetric-memory block with a multicast mapping (the switch reduces; multimem kernel)
+        for kind, mc in (("sgd", False), ("adam", False), ("sgd", None), ("adam", None)):
             for n, one_shot in [(q, 0), (q, 1), (256 * q, 1), (1000 * q, 0), (8 * 1024 * 1024, 0)]:
+                if mc is None and one_shot:
+                    continue
                 nbytes = (n * es + 511) // 512 * 512
-                comm = Communicator(heap_bytes=2 * nbytes)
+                comm = Communicator(heap_bytes=2 * nbytes, multicast=mc)
+                if mc is None:
+                    worst["nvls"] = float(comm.multicast)
                 grad, param = comm.heap_view(0, n, dtype), comm.heap_view(nbytes, n, dtype)
                 torch.manual_seed(7)
                 p0 = torch.randn(n, device="cuda")
@@ -178,7 +184,7 @@ def _w_allreduce():
                 dist.barrier()
                 comm.destroy()
     dist.destroy_process_group()
-    return {"%s_%s" % k: v for k, v in worst.items()}
+    return {("%s_%s" % k if isinstance(k, tuple) else k): v for k, v in worst.items()}
 
 
 def _w_ddp_config1(steps):
@@ -239,7 +245,8 @@ def _w_ddp_syncbn_vs_torch():
     base = workloads.cifar_resnet18(10).cuda()
     ref = torch.nn.parallel.DistributedDataParallel(torch.nn.SyncBatchNorm.convert_sync_batchnorm(copy.deepcopy(base)),
                                                     device_ids=[rank])
-    ours = b200.B200DDP(b200.fuse_bn_relu(b200.convert_sync_batchnorm(copy.deepcopy(base))), device_ids=[rank])
+    ours = b200.B200DDP(b200.fuse_bn_relu(b200.convert_sync_batchnorm(copy.deepcopy(base))), device_ids=[rank],
+                        nvls="auto")   # the switch-reduced bucket kernel where the platform has NVLS, else peer loads
     o_ref = torch.optim.SGD(ref.parameters(), lr=1e-3, momentum=0.5)
     o_our = ours.fuse_optimizer(torch.optim.SGD(ours.parameters(), lr=1e-3, momentum=0.5), materialize_grads=True)
     for step in range(8):

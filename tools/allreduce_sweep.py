@@ -44,6 +44,7 @@ def main():
     world = dist.get_world_size()
     lib = _lib.lib()
     max_bytes = int(os.environ.get("SWEEP_MAX_BYTES", 256 << 20))
+    nvls = os.environ.get("SWEEP_NVLS", "0") == "1"   # heap with a multicast mapping: the two-shot kernel reduces in the switch
     rows = []
     for dtype in (torch.float32, torch.bfloat16):
         code, es = _lib.dtype_code(dtype), (2 if dtype == torch.bfloat16 else 4)
@@ -51,7 +52,7 @@ def main():
         while size <= max_bytes:
             n = max(size // es, 8 * world) // (8 * world) * (8 * world)
             nbytes = (n * es + 511) // 512 * 512
-            comm = Communicator(heap_bytes=2 * nbytes)
+            comm = Communicator(heap_bytes=2 * nbytes, multicast=True if nvls else False)
             grad, param = comm.heap_view(0, n, dtype), comm.heap_view(nbytes, n, dtype)
             grad.normal_(); param.normal_()
             master = param.float() if dtype == torch.bfloat16 else None
@@ -86,10 +87,11 @@ def main():
 
             res["nccl_allreduce_only"] = timed(nccl_only, 20 if size <= (16 << 20) else 8, world, dev)
             comm.check_error()
+            comm_multicast = comm.multicast
             comm.destroy()
             if rank == 0:
                 bus = lambda ms: n * es / (ms / 1e3) * 2 * (world - 1) / world / 1e9  # noqa: E731
-                row = {"dtype": str(dtype).split(".")[-1], "bytes": n * es, "world": world,
+                row = {"dtype": str(dtype).split(".")[-1], "bytes": n * es, "world": world, "nvls": bool(comm_multicast),
                        **{k + "_us": round(v * 1e3, 2) for k, v in res.items()},
                        **{k + "_busGBs": round(bus(v), 1) for k, v in res.items()}}
                 rows.append(row)
