@@ -207,7 +207,10 @@ class B200DDP(DistributedDataParallel):
             # in the environment ("1", "auto", anything else or unset = off)
             if nvls is None:
                 nvls = {"1": True, "auto": "auto"}.get(os.environ.get("B200DP_NVLS", "0"), False)
-            multicast = None if nvls == "auto" else bool(nvls)
+            if nvls == "auto":   # the switch reduction pays from 4 ranks on (at 2 it moves more bytes than peer loads)
+                multicast = None if self.world >= 4 else False
+            else:
+                multicast = bool(nvls)
             self.comm = Communicator(process_group, heap_bytes=heap, device=self.device, multicast=multicast)
             self._comm_stream = torch.cuda.Stream(device=self.device)
         self._param_index = {}

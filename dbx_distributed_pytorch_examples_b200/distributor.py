@@ -17,6 +17,7 @@ from __future__ import annotations
 import multiprocessing as mp
 import os
 import socket
+import time
 import traceback
 
 import cloudpickle
@@ -55,6 +56,7 @@ class TorchDistributor:
         self.num_processes = num_processes
         self.local_mode = local_mode
         self.use_gpu = use_gpu
+        self.failure_grace_s = 10.0
 
     def run(self, train_object, *args, **kwargs):
         if not callable(train_object):
@@ -71,18 +73,38 @@ class TorchDistributor:
             child.close()
             procs.append(p)
             conns.append(parent)
+        # Collect the results as they come.  Once one rank has failed the others get a few seconds to report
+        # and are then terminated (what torchrun's elastic agent does): a rank blocked in a collective with a
+        # dead peer would otherwise sit there until the backend's own timeout (10 minutes for NCCL).
+        from multiprocessing.connection import wait as _wait
+
         results, errors = [None] * self.num_processes, []
-        for rank, (p, c) in enumerate(zip(procs, conns)):
-            try:
-                status, body = c.recv()
-            except EOFError:
-                status, body = "error", f"rank {rank}: worker exited without a result"
-            if status == "ok":
-                results[rank] = body
-            else:
-                errors.append(body)
+        pending = {c: rank for rank, c in enumerate(conns)}
+        deadline = None
+        while pending:
+            timeout = None if deadline is None else max(0.0, deadline - time.monotonic())
+            ready = _wait(list(pending), timeout=timeout)
+            if not ready:  # grace period after a failure is over
+                for c, rank in pending.items():
+                    procs[rank].terminate()
+                    errors.append(f"rank {rank}: terminated after another rank failed")
+                break
+            for c in ready:
+                rank = pending.pop(c)
+                try:
+                    status, body = c.recv()
+                except EOFError:
+                    status, body = "error", f"rank {rank}: worker exited without a result"
+                if status == "ok":
+                    results[rank] = body
+                else:
+                    errors.append(body)
+                    if deadline is None:
+                        deadline = time.monotonic() + self.failure_grace_s
         for p in procs:
-            p.join()
+            p.join(timeout=30)
+            if p.is_alive():
+                p.kill()
         if errors:
             raise RuntimeError("TorchDistributor worker failed:\n" + "\n".join(errors))
         return cloudpickle.loads(results[0])
