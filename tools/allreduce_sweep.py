@@ -61,7 +61,7 @@ def main():
             o.kind, o.lr, o.momentum = _lib.OPT_SGD, 1e-3, 0.5
             stream = _lib.current_stream()
             res = {}
-            for label, one_shot, ctas in (("two_shot", 0, 64), ("two_shot_148", 0, 148), ("one_shot", 1, 64)):
+            for label, one_shot, ctas in (("two_shot_32", 0, 32), ("two_shot", 0, 64), ("two_shot_148", 0, 148), ("one_shot", 1, 64)):
                 if one_shot and size > (4 << 20):
                     continue
 

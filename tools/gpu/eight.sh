@@ -3,7 +3,7 @@ N=$1
 export B200DP_TIMEOUT_S=30
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29611"
 nvidia-smi topo -m > gpurun_out/r2_topo_n$N.txt 2>&1
-timeout -k 5 420 python -m pytest tests/test_gpu_multi.py -m gpu -q -s -p no:cacheprovider -k "$N]" > gpurun_out/r2_multi_n$N.log 2>&1
+timeout -k 5 420 python -m pytest tests/test_gpu_multi.py -m gpu -v -s -p no:cacheprovider -k "$N" > gpurun_out/r2_multi_n$N.log 2>&1
 grep -v "frame #\|should dump\|^$\|Exception raised from\|recvValue\|sendBytes\|c10::Error\|unknown function\|UserWarning\|Consider using\|key = (\|moved = float" gpurun_out/r2_multi_n$N.log | tail -25
 timeout -k 5 200 $TR tools/allreduce_sweep.py > gpurun_out/r2_allreduce_sweep_n$N.jsonl 2> gpurun_out/r2_allreduce_sweep_n$N.err
 SWEEP_NVLS=1 timeout -k 5 200 $TR tools/allreduce_sweep.py > gpurun_out/r2_allreduce_sweep_nvls_n$N.jsonl 2> gpurun_out/r2_allreduce_sweep_nvls_n$N.err
