@@ -498,9 +498,12 @@ extern "C" int b200dp_allreduce_update(b200dp_comm* comm, size_t grad_heap_off, 
   const b200dp_peers P = b200dp_make_peers(comm);
   cudaStream_t s = (cudaStream_t)stream;
   if (world > 1 && !one_shot && comm->heap_mc && nvls_enabled() && grad_dtype == param_dtype) {
-    // each thread keeps kNvlsUnroll reductions in flight: fewer CTAs are wanted for the same range
+    // each thread keeps kNvlsUnroll reductions in flight, and the switch does the fan-in: 32 CTAs already
+    // saturate the links (profiles/r2_allreduce_sweep_nvls_n8.jsonl: 714 GB/s bus at 64 MB with 32 CTAs, 683
+    // with 64, 614 with 148), so that is the library default
     long long want4 = (units + (long long)kT * kNvlsUnroll - 1) / ((long long)kT * kNvlsUnroll);
-    int g4 = (int)(want4 < 1 ? 1 : (want4 > cap ? cap : want4));
+    const int cap4 = max_ctas > 0 ? cap : 32;
+    int g4 = (int)(want4 < 1 ? 1 : (want4 > cap4 ? cap4 : want4));
     return grad_dtype == B200DP_F32 ? launch_nvls<float>(A, P, g4, s) : launch_nvls<__nv_bfloat16>(A, P, g4, s);
   }
   if (grad_dtype == B200DP_F32 && param_dtype == B200DP_F32)
