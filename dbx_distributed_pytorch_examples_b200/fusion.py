@@ -108,7 +108,8 @@ def unfuse_bn_relu(model: nn.Module) -> nn.Module:
                 bn = getattr(m, name, None)
                 if _is_ours(bn):
                     bn.fuse_relu = False
-        elif _looks_like_resnet_stem(m) and isinstance(m.relu, nn.Identity) and m.bn1.fuse_relu:
+        elif (all(hasattr(m, a) for a in ("conv1", "bn1", "relu", "maxpool", "layer1", "fc")) and _is_ours(m.bn1)
+              and isinstance(m.relu, nn.Identity) and m.bn1.fuse_relu):   # a stem that fuse_bn_relu rewired
             m.bn1.fuse_relu = False
             m.relu = nn.ReLU(inplace=True)
             if isinstance(m.maxpool, pool.B200MaxPool2d):

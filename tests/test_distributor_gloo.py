@@ -61,6 +61,25 @@ def test_worker_errors_propagate():
         TorchDistributor(num_processes=2, use_gpu=False).run(boom)
 
 
+def test_one_failing_rank_does_not_strand_the_others():
+    """Rank 0 raises while rank 1 is stuck (as it would be inside a collective with a dead peer): the launcher
+    reports rank 0's error and terminates rank 1 after a short grace period instead of waiting for it."""
+    import time
+
+    def fn():
+        if int(os.environ["RANK"]) == 0:
+            raise ValueError("rank 0 gave up")
+        time.sleep(600)
+
+    d = TorchDistributor(num_processes=2, use_gpu=False)
+    d.failure_grace_s = 2.0
+    t0 = time.monotonic()
+    with pytest.raises(RuntimeError, match="rank 0 gave up") as info:
+        d.run(fn)
+    assert time.monotonic() - t0 < 120
+    assert "rank 1: terminated after another rank failed" in str(info.value)
+
+
 def test_deepspeed_flavour_signature():
     d = DeepspeedTorchDistributor(numGpus=1, nnodes=1, localMode=True, useGpu=False)
     assert d.run(lambda a, b=0: a + b, 1, b=2) == 3

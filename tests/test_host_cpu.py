@@ -142,6 +142,24 @@ def test_convert_and_fuse_keep_state_dict_layout():
     assert out.conv1.weight.dtype == torch.bfloat16
 
 
+def test_unfuse_restores_the_plain_modules():
+    """fuse_bn_relu -> unfuse_bn_relu is the identity on the module structure (B200DDP pickles the unfused form:
+    a block whose forward is an instance attribute cannot be unpickled)."""
+    import pickle
+    for make in (lambda: workloads.cifar_resnet18(10), lambda: workloads.resnet50(10)):
+        m = b200.fuse_bn_relu(b200.convert_sync_batchnorm(make()))
+        assert any("forward" in mod.__dict__ for mod in m.modules())
+        keys = list(m.state_dict())
+        m = b200.unfuse_bn_relu(m)
+        assert not any("forward" in mod.__dict__ for mod in m.modules())
+        assert not any(getattr(mod, "fuse_relu", False) for mod in m.modules())
+        assert isinstance(m.relu, nn.ReLU) and type(m.maxpool) is nn.MaxPool2d
+        assert list(m.state_dict()) == keys
+        back = pickle.loads(pickle.dumps(m))
+        assert list(back.state_dict()) == keys
+        assert b200.fuse_bn_relu(back).bn1.fuse_relu          # and it fuses again
+
+
 def test_torchvision_resnet50_is_recognised():
     model = b200.fuse_bn_relu(b200.convert_sync_batchnorm(workloads.resnet50(10)))
     bns = [m for m in model.modules() if isinstance(m, b200.B200SyncBatchNorm)]
