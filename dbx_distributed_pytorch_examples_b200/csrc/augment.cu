@@ -1,20 +1,19 @@
 // augment.cu — uint8 NHWC -> random-crop / h-flip / normalize -> bf16 NHWC.
 //
-// One persistent kernel over (image, row-tile) tiles:
-//   * the source rows of a tile are staged into shared memory with 16-byte
-//     cp.async from the aligned-down address (double buffered, so the next
-//     tile's loads are in flight while this tile is being written out);
-//   * the normalisation is a lookup: there are only 3*256 possible results of
-//     ((v/255) - mean[c]) / std[c], so they are computed once per CTA with the
-//     same two IEEE fp32 operations torchvision performs and replicated 32x in
-//     shared memory, one copy per bank, which makes every lookup conflict-free
-//     whatever the pixel values are;
-//   * every thread produces 8 pixels (24 bf16 outputs, three 128-bit stores); crop
-//     offset, flip and zero padding are index arithmetic on the staged bytes, with
-//     everything per-element folded to compile-time constants.
-// When the host finds that one fp32 FMA per element reproduces the table bit for bit (it
-// does for the usual ImageNet / CIFAR statistics), a table-free variant of the kernel runs
-// instead (see "arithmetic fast path" below).
+// Three kernels, all bit-exact with torchvision's two fp32 steps ((v/255) - mean[c]) / std[c]:
+//   * augment_direct_kernel (the DEFAULT, taken whenever a source row is a whole number of 32-bit
+//     words and the host has verified over all 3*256 inputs that one fp32 FMA per element rounds to the
+//     same bf16 as the two steps — true for the ImageNet and CIFAR statistics): no staging and no
+//     barriers; a thread fetches the <= 7 aligned words that hold its 8 source pixels through L1 and
+//     writes three 128-bit stores; 6 CTAs x 256 threads per SM.
+//   * augment_affine_kernel: the same arithmetic for sources the direct kernel does not take;
+//     persistent over (image, row-tile) tiles, source rows staged with 16-byte cp.async from the
+//     aligned-down address, double buffered.
+//   * augment_kernel: for statistics where the FMA form is NOT exact, the normalisation is a lookup:
+//     the 3*256 possible results are computed once per CTA with torchvision's two operations and
+//     replicated 32x in shared memory (one copy per bank, conflict-free whatever the pixel values).
+// In all of them a thread produces 8 pixels (24 bf16 outputs); crop offset, flip and zero padding are
+// index arithmetic with everything per-element folded to compile-time constants.
 // Algorithmic traffic: 1 B read + 2 B written per output element.
 #include <math.h>
 #include <stdlib.h>

@@ -5,7 +5,8 @@
   [64,128,256,512] x 2, 1x1-conv+BN projection on a shape change).  The module
   tree uses the same attribute names, so ``state_dict`` keys, parameter
   registration order and the RNG consumed by a seeded construction are those
-  of the reference class (checked by tests/test_workloads.py when the
+  of the reference class (checked by
+  tests/test_host_cpu.py::test_workload_matches_reference_model when the
   reference is mounted).
 * :func:`resnet50` — torchvision's ResNet-50, the model of
   01_torch_distributor/03_tiny_imagenet_torch_distributor_resnet.py:125-143 and
