@@ -301,3 +301,22 @@ def test_bucket_plan_invariants_property():
             assert ours == ddp_ref.bucket_assignment(padded, cap=cap_mb * 1024 * 1024)
 
     check()
+
+
+def test_reference_arm_of_the_bench_prints_the_contract_line():
+    """`bench.py --impl reference` (the CPU arm the driver runs beside every GPU number): stock DDP over gloo with
+    two ranks on the host cores, bounded steps, one JSON line with the contract's keys and no GPU launches."""
+    import json
+    import subprocess
+    import sys
+    env = {k: v for k, v in os.environ.items() if k not in ("RANK", "LOCAL_RANK", "WORLD_SIZE")}
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "1"],
+                         capture_output=True, text=True, stdin=subprocess.DEVNULL, timeout=900, env=env)
+    assert out.returncode == 0, out.stderr[-2000:]
+    line = json.loads([l for l in out.stdout.splitlines() if l.startswith("{")][-1])
+    assert line["impl"] == "reference" and line["unit"] == "images/s" and line["value"] > 0
+    assert line["gpu_launches"] == 0 and line["higher_is_better"] is True
+    assert line["config"]["parallelism"] == "cpu-gloo-2" and line["config"]["workload"] == "resnet50_224_syncbn_ddp_augment"
+    cb = line["cpu_baseline"]
+    assert cb["kind"] == "reference" and cb["cores"] >= 2 and "2 ranks" in cb["sample"] and cb["value"] == line["value"]
+    assert line["e2e"] == {"value": line["value"], "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
