@@ -2,6 +2,8 @@
 // exchange by peer stores, fused BN(+residual)+ReLU forward and backward.
 //
 // Data layout.  An activation is [M, C] row-major (channels_last), M = N*H*W.
+//
+// Two-kernel path (every layer that does not qualify for the one-kernel path below).
 // A CTA of 256 threads is 32 rows x 8 sixteen-byte vectors: it owns one
 // 128-byte channel chunk (64 bf16 / 32 fp32 channels) and walks down the rows,
 // so every warp request is four full 128-byte lines and every thread keeps the
@@ -11,13 +13,16 @@
 // Rows are staged through per-thread shared-memory rings filled by cp.async, so
 // each thread has 4-8 rows per input in flight (RowRing below).
 //
-// Reductions (stats, backward sums): thread -> CTA tree in shared memory ->
-// per-CTA partial in `scratch` -> the last CTA of each chunk (ticket counter)
-// merges the partials, writes the rank-local result and, when world > 1,
-// stores it into every peer's exchange slot and raises that chunk's flag
-// (st.release.sys).  The element-wise kernels that follow start by waiting on
-// the flags of their own chunk, merge the ranks' vectors in rank order (so all
-// ranks get bit-identical statistics) and stream.
+// Reductions (stats, backward sums): thread -> warp shuffles over the rows of a warp ->
+// the 8 warp partials through shared memory -> the 8 CTAs of a cluster through DSMEM ->
+// one partial per cluster in `scratch` -> the last cluster leader of each chunk (ticket
+// counter) merges the partials, writes the rank-local result and, when world > 1, the
+// whole CTA stores it into every peer's exchange slot as LL words {value, seq}.  The
+// element-wise kernels that follow poll the words of their own chunk, merge the ranks'
+// vectors in rank order (so all ranks get bit-identical statistics) and stream.
+//
+// One-kernel path (b200dp_bn_forward / b200dp_bn_backward on wide, short layers): one
+// thread-block cluster per channel chunk does both passes; see "one kernel per direction".
 //
 // Algorithmic traffic per element (bf16): stats 2 B; fwd apply 4 B (+2 with a
 // residual); bwd reduce 4 B; bwd apply 6 B (+2 for d_residual); the ReLU mask
